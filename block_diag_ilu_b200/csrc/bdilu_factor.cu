@@ -1,0 +1,289 @@
+// Kernel 1: batched per-block LU with partial pivoting + sub/bot scaling + permutation vectors.
+//
+// Replaces ILU_inplace<double>::ILU_inplace (block_diag_ilu.hpp:430-485) and the dgetrf_ it calls
+// (anyode_blas_lapack.hpp:55-57).  One G-lane group (G = blockw rounded up to a power of two, 32/G
+// blocks per warp) owns one diagonal block; lane r keeps ROW r of the block in registers.
+//
+// Pivoting is implicit: rows never move between lanes.  Each lane tracks `pos`, the position its row
+// currently occupies in LAPACK's swapped ordering, so that
+//   * the pivot of step k is the candidate of maximum modulus with the LOWEST current position
+//     (idamax's "first maximum" rule, which is what makes ipiv bit-exact),
+//   * ipiv[k] = (position of the chosen row) + 1, and the row that sat at position k takes its place,
+//   * at the end lane r stores its row at row `pos` of the column-major block: the stored L\U is
+//     LAPACK's in-place layout, rowbycol[pos] = r, colbyrow[r] = pos (block_diag_ilu.hpp:34-52).
+// The arithmetic on each element is the right-looking elimination of dgetf2 / anyode_blasless.hpp:
+// l = a/piv by true division, a -= l*u.
+#include "bdilu_common.cuh"
+#include "bdilu_kernels.h"
+
+namespace bdilu {
+
+constexpr int FACTOR_WARPS = 4;
+
+// argmax of v over the group with ties broken towards the lowest `pos`; returns the winning lane
+// (group-local index).  Inactive lanes pass v = -1.
+template <int G>
+__device__ __forceinline__ int group_argmax(double v, int pos, int r)
+{
+    if (G == 32) {
+        // |x| >= 0 orders like its bit pattern: reduce the high word, then the low word among ties.
+        const int hi = __double2hiint(v);
+        const unsigned lo = (unsigned)__double2loint(v);
+        const int mhi = __reduce_max_sync(FULL, hi);
+        const bool c1 = (hi == mhi);
+        const unsigned mlo = __reduce_max_sync(FULL, c1 ? lo : 0u);
+        const bool c2 = c1 && (lo == mlo);
+        unsigned bal = __ballot_sync(FULL, c2);
+        if (__popc(bal) > 1) {
+            const unsigned mp = __reduce_min_sync(FULL, c2 ? (unsigned)pos : 0xffffu);
+            bal = __ballot_sync(FULL, c2 && (unsigned)pos == mp);
+        }
+        return __ffs(bal) - 1;
+    } else {
+        int win = r;
+#pragma unroll
+        for (int off = G / 2; off > 0; off >>= 1) {
+            const double v2 = group_bcast<G>(v, r ^ off);
+            const int p2 = __shfl_sync(FULL, pos, r ^ off, G);
+            const int w2 = __shfl_sync(FULL, win, r ^ off, G);
+            if (v2 > v || (v2 == v && p2 < pos)) { v = v2; pos = p2; win = w2; }
+        }
+        return win;
+    }
+}
+
+template <int WP>
+__global__ void __launch_bounds__(FACTOR_WARPS * 32)
+factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
+              int *__restrict__ ipiv, int *__restrict__ rowbycol, int *__restrict__ colbyrow,
+              int *__restrict__ info)
+{
+    constexpr int G = WP;
+    constexpr int BPW = 32 / G;
+    // pivot-row mailbox: [warp][group][2 buffers][WP]
+    __shared__ __align__(16) double urow_s[FACTOR_WARPS][BPW][2][WP];
+
+    const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+    const int grp = lane / G, r = lane % G;
+    const int w = D.w, ld = D.ld;
+    const int64_t total = (int64_t)nsys * D.nblocks;
+    int64_t gb = ((int64_t)blockIdx.x * FACTOR_WARPS + wic) * BPW + grp;
+    const bool live = gb < total;  // dead groups run on the last block but store nothing
+    if (!live) gb = total - 1;
+    const int sys = (int)(gb / D.nblocks), bi = (int)(gb % D.nblocks);
+    double *sysdata = data + (int64_t)sys * sys_stride;
+    double *blk = sysdata + D.block(bi);
+    const bool rowok = r < w;
+
+    // row r of the block; rows/columns beyond w are padded with the identity
+    double a[WP];
+#pragma unroll
+    for (int c = 0; c < WP; ++c)
+        a[c] = (rowok && c < w) ? ld_stream(blk + (int64_t)c * ld + r) : ((c == r) ? 1.0 : 0.0);
+
+    double (*urow)[WP] = urow_s[wic][grp];
+    int pos = r;          // current position of my row in the swapped ordering
+    bool active = rowok;  // not yet chosen as a pivot row
+    int my_ipiv = r + 1;  // lane k keeps ipiv[k]
+    double my_diag = 1.0; // lane k keeps U[k][k]
+    int my_info = 0;
+
+#pragma unroll
+    for (int k = 0; k < WP; ++k) {
+        if (k < w) {
+            const double v = active ? fabs(a[k]) : -1.0;
+            const int p = group_argmax<G>(v, pos, r);
+            const int q = __shfl_sync(FULL, pos, p, G);
+            if (r == k) my_ipiv = q + 1;
+            if (pos == k) pos = q;
+            if (r == p) { pos = k; active = false; }
+
+            // publish the pivot row (columns k..WP-1) to the group
+            double2 *u2w = reinterpret_cast<double2 *>(urow[k & 1]);
+            if (r == p) {
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
+            }
+            __syncwarp();
+            const double2 *u2 = reinterpret_cast<const double2 *>(urow[k & 1]);
+            double u[WP];
+#pragma unroll
+            for (int m = k / 2; m < WP / 2; ++m) {
+                const double2 t = u2[m];
+                u[2 * m] = t.x;
+                u[2 * m + 1] = t.y;
+            }
+            const double piv = u[k];
+            if (r == k) my_diag = piv;
+            if (piv == 0.0) {
+                if (my_info == 0) my_info = k + 1;  // dgetf2: record, leave the column unscaled
+            } else if (active) {
+                const double l = a[k] / piv;  // true division: the reference tests exact quotients
+                a[k] = l;
+#pragma unroll
+                for (int j = k + 1; j < WP; ++j) a[j] = fma(-l, u[j], a[j]);
+            }
+        }
+    }
+
+    if (live && rowok) {
+#pragma unroll
+        for (int c = 0; c < WP; ++c)
+            if (c < w) blk[(int64_t)c * ld + pos] = a[c];
+        const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
+        ipiv[ib + r] = my_ipiv;
+        rowbycol[ib + pos] = r;
+        colbyrow[ib + r] = pos;
+        // sub(di,bi,c) /= U[c][c]  (block_diag_ilu.hpp:471-475)
+        for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
+            double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
+            *s = *s / my_diag;
+        }
+        // bot(sati,bi,c) /= U[c][c]  (:476-479)
+        if (bi < D.nsat)
+            for (int sati = bi; sati < D.nsat; ++sati) {
+                double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
+                *s = *s / my_diag;
+            }
+        if (my_info != 0 && r == 0) {
+            // keep the failing block with the lowest index (serial loop order, :469-470)
+            const int key = (bi << 7) | my_info;
+            int old = atomicCAS(&info[sys], 0, key);
+            while (old != 0 && (old >> 7) > bi) {
+                const int assumed = old;
+                old = atomicCAS(&info[sys], assumed, key);
+                if (old == assumed) break;
+            }
+        }
+    }
+}
+
+// 32 < blockw <= 64: one 64-thread CTA per block, thread r keeps row r (64 doubles) in registers.
+// Same algorithm; the pivot search and the pivot-row mailbox cross the two warps through shared
+// memory and __syncthreads().
+__global__ void __launch_bounds__(64)
+factor_wide_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
+                   int *__restrict__ ipiv, int *__restrict__ rowbycol, int *__restrict__ colbyrow,
+                   int *__restrict__ info)
+{
+    constexpr int WP = 64;
+    __shared__ __align__(16) double urow[2][WP];
+    __shared__ double cand_v[2][2];
+    __shared__ int cand_pos[2][2], cand_row[2][2];
+
+    const int r = threadIdx.x, lane = r & 31, wid = r >> 5;
+    const int w = D.w, ld = D.ld;
+    const int64_t gb = blockIdx.x;
+    const int sys = (int)(gb / D.nblocks), bi = (int)(gb % D.nblocks);
+    double *sysdata = data + (int64_t)sys * sys_stride;
+    double *blk = sysdata + D.block(bi);
+    const bool rowok = r < w;
+
+    double a[WP];
+#pragma unroll
+    for (int c = 0; c < WP; ++c)
+        a[c] = (rowok && c < w) ? ld_stream(blk + (int64_t)c * ld + r) : ((c == r) ? 1.0 : 0.0);
+
+    int pos = r;
+    bool active = rowok;
+    int my_ipiv = r + 1;
+    double my_diag = 1.0;
+    int my_info = 0;
+
+#pragma unroll
+    for (int k = 0; k < WP; ++k) {
+        if (k < w) {
+            const double v = active ? fabs(a[k]) : -1.0;
+            const int pl = group_argmax<32>(v, pos, lane);  // winner inside my warp
+            if (lane == pl) { cand_v[k & 1][wid] = v; cand_pos[k & 1][wid] = pos; cand_row[k & 1][wid] = r; }
+            __syncthreads();
+            const double v0 = cand_v[k & 1][0], v1 = cand_v[k & 1][1];
+            const int p0 = cand_pos[k & 1][0], p1 = cand_pos[k & 1][1];
+            const bool take1 = (v1 > v0) || (v1 == v0 && p1 < p0);
+            const int p = take1 ? cand_row[k & 1][1] : cand_row[k & 1][0];
+            const int q = take1 ? p1 : p0;
+            if (r == k) my_ipiv = q + 1;
+            if (pos == k) pos = q;
+            if (r == p) { pos = k; active = false; }
+
+            double2 *u2w = reinterpret_cast<double2 *>(urow[k & 1]);
+            if (r == p) {
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
+            }
+            __syncthreads();
+            const double2 *u2 = reinterpret_cast<const double2 *>(urow[k & 1]);
+            const double piv = urow[k & 1][k];
+            if (r == k) my_diag = piv;
+            if (piv == 0.0) {
+                if (my_info == 0) my_info = k + 1;
+            } else if (active) {
+                const double l = a[k] / piv;
+                a[k] = l;
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) {
+                    const double2 t = u2[m];
+                    if (2 * m > k) a[2 * m] = fma(-l, t.x, a[2 * m]);
+                    if (2 * m + 1 > k) a[2 * m + 1] = fma(-l, t.y, a[2 * m + 1]);
+                }
+            }
+        }
+    }
+
+    if (rowok) {
+#pragma unroll
+        for (int c = 0; c < WP; ++c)
+            if (c < w) blk[(int64_t)c * ld + pos] = a[c];
+        const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
+        ipiv[ib + r] = my_ipiv;
+        rowbycol[ib + pos] = r;
+        colbyrow[ib + r] = pos;
+        for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
+            double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
+            *s = *s / my_diag;
+        }
+        if (bi < D.nsat)
+            for (int sati = bi; sati < D.nsat; ++sati) {
+                double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
+                *s = *s / my_diag;
+            }
+        if (my_info != 0 && r == 0) {
+            const int key = (bi << 7) | my_info;
+            int old = atomicCAS(&info[sys], 0, key);
+            while (old != 0 && (old >> 7) > bi) {
+                const int assumed = old;
+                old = atomicCAS(&info[sys], assumed, key);
+                if (old == assumed) break;
+            }
+        }
+    }
+}
+
+cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
+                          int *rowbycol, int *colbyrow, int *info, cudaStream_t st)
+{
+    const int64_t total = (int64_t)nsys * D.nblocks;
+    if (total == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int) * (size_t)nsys, st);
+    if (e != cudaSuccess) return e;
+#define BDILU_LAUNCH_FACTOR(WP)                                                                    \
+    {                                                                                              \
+        const int64_t per_cta = (int64_t)FACTOR_WARPS * (32 / WP);                                 \
+        const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);                         \
+        factor_kernel<WP><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv,     \
+                                                              rowbycol, colbyrow, info);           \
+    }
+    const int w = D.w;
+    if (w <= 2) BDILU_LAUNCH_FACTOR(2)
+    else if (w <= 4) BDILU_LAUNCH_FACTOR(4)
+    else if (w <= 8) BDILU_LAUNCH_FACTOR(8)
+    else if (w <= 16) BDILU_LAUNCH_FACTOR(16)
+    else if (w <= 32) BDILU_LAUNCH_FACTOR(32)
+    else factor_wide_kernel<<<(unsigned)total, 64, 0, st>>>(data, sys_stride, nsys, D, ipiv, rowbycol,
+                                                             colbyrow, info);
+#undef BDILU_LAUNCH_FACTOR
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+}  // namespace bdilu

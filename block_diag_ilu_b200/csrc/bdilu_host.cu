@@ -1,0 +1,247 @@
+// Host-pointer entry points of the C ABI: own the device mirrors, marshal H2D/D2H, block until done.
+// These are what the C++ header shim (include/block_diag_ilu_b200.hpp) and the Python wrapper bind
+// when the caller's data lives in host memory, as it always does in the reference.
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/bdilu.h"
+#include "bdilu_kernels.h"
+
+using namespace bdilu;
+
+struct bdilu_ilu {
+    int nsys, nblocks, blockw, ndiag, nsat, ld;
+    int64_t sys_stride;  // device stride == host stride
+    double *d_data = nullptr;
+    int *d_ipiv = nullptr, *d_rowbycol = nullptr, *d_colbyrow = nullptr, *d_info = nullptr;
+    double *d_b = nullptr, *d_x = nullptr;  // grown on demand by solve
+    int *d_flags = nullptr;
+    size_t vec_cap = 0, flag_cap = 0;
+    cudaStream_t st = nullptr;
+};
+
+namespace {
+
+// device entry points report through bdilu_last_error(); host ones reuse that channel
+int set_err(int code, const std::string &msg);
+
+#define CUH(call)                                                                        \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            cudaGetLastError();                                                          \
+            return set_err(BDILU_ERR_CUDA, std::string(#call ": ") + cudaGetErrorString(e_)); \
+        }                                                                                \
+    } while (0)
+
+thread_local std::string t_host_err;
+int set_err(int code, const std::string &msg)
+{
+    t_host_err = msg;
+    bdilu::set_last_error(t_host_err.c_str());
+    return code;
+}
+
+void free_handle(bdilu_ilu *h)
+{
+    if (!h) return;
+    cudaFree(h->d_data); cudaFree(h->d_ipiv); cudaFree(h->d_rowbycol); cudaFree(h->d_colbyrow);
+    cudaFree(h->d_info); cudaFree(h->d_b); cudaFree(h->d_x); cudaFree(h->d_flags);
+    if (h->st) cudaStreamDestroy(h->st);
+    delete h;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bdilu_ilu_create(bdilu_ilu **out, double *host_data, int64_t sys_stride, int nsys, int nblocks, int blockw,
+                     int ndiag, int nsat, int ld, int copy_back, int *ipiv, int *rowbycol, int *colbyrow, int *info)
+{
+    if (!out) return set_err(BDILU_ERR_ARG, "out is null");
+    *out = nullptr;
+    if (nsys < 1 || !host_data) return set_err(BDILU_ERR_ARG, "nsys < 1 or null data");
+    if (ld == 0) ld = bdilu_default_ld(blockw);
+    const int64_t nd = bdilu_ndata(nblocks, blockw, ndiag, nsat, ld);
+    if (nsys == 1) sys_stride = nd;
+    if (bdilu_device_count() < 1) return set_err(BDILU_ERR_CUDA, "no CUDA device: libbdilu_b200 has no CPU fallback");
+    bdilu_ilu *h = new (std::nothrow) bdilu_ilu;
+    if (!h) return set_err(BDILU_ERR_ARG, "out of host memory");
+    h->nsys = nsys; h->nblocks = nblocks; h->blockw = blockw; h->ndiag = ndiag; h->nsat = nsat; h->ld = ld;
+    h->sys_stride = sys_stride;
+    const size_t nbytes = sizeof(double) * (size_t)((int64_t)(nsys - 1) * sys_stride + nd);
+    const size_t nidx = (size_t)nsys * nblocks * blockw;
+#define CUC(call)                                                                                      \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            free_handle(h);                                                                            \
+            cudaGetLastError();                                                                        \
+            return set_err(BDILU_ERR_CUDA, std::string(#call ": ") + cudaGetErrorString(e_));          \
+        }                                                                                              \
+    } while (0)
+    CUC(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    CUC(cudaMalloc(&h->d_data, nbytes ? nbytes : 8));
+    CUC(cudaMalloc(&h->d_ipiv, sizeof(int) * (nidx ? nidx : 1)));
+    CUC(cudaMalloc(&h->d_rowbycol, sizeof(int) * (nidx ? nidx : 1)));
+    CUC(cudaMalloc(&h->d_colbyrow, sizeof(int) * (nidx ? nidx : 1)));
+    CUC(cudaMalloc(&h->d_info, sizeof(int) * (size_t)nsys));
+    CUC(cudaMemcpyAsync(h->d_data, host_data, nbytes, cudaMemcpyHostToDevice, h->st));
+    int rc = bdilu_factor(h->d_data, sys_stride, nsys, nblocks, blockw, ndiag, nsat, ld, h->d_ipiv, h->d_rowbycol,
+                          h->d_colbyrow, h->d_info, h->st);
+    if (rc) { free_handle(h); return rc; }
+    if (copy_back) CUC(cudaMemcpyAsync(host_data, h->d_data, nbytes, cudaMemcpyDeviceToHost, h->st));
+    if (ipiv) CUC(cudaMemcpyAsync(ipiv, h->d_ipiv, sizeof(int) * nidx, cudaMemcpyDeviceToHost, h->st));
+    if (rowbycol) CUC(cudaMemcpyAsync(rowbycol, h->d_rowbycol, sizeof(int) * nidx, cudaMemcpyDeviceToHost, h->st));
+    if (colbyrow) CUC(cudaMemcpyAsync(colbyrow, h->d_colbyrow, sizeof(int) * nidx, cudaMemcpyDeviceToHost, h->st));
+    if (info) CUC(cudaMemcpyAsync(info, h->d_info, sizeof(int) * (size_t)nsys, cudaMemcpyDeviceToHost, h->st));
+    CUC(cudaStreamSynchronize(h->st));
+#undef CUC
+    *out = h;
+    return BDILU_OK;
+}
+
+int bdilu_ilu_solve(bdilu_ilu *h, const double *host_b, double *host_x, int nrhs, int *flags)
+{
+    if (!h || !host_b || !host_x || nrhs < 1) return set_err(BDILU_ERR_ARG, "null handle/pointer or nrhs < 1");
+    const int64_t n = (int64_t)h->nblocks * h->blockw;
+    const size_t nvec = (size_t)h->nsys * nrhs;
+    const size_t vbytes = sizeof(double) * nvec * (size_t)n;
+    if (vbytes > h->vec_cap) {
+        cudaFree(h->d_b); cudaFree(h->d_x);
+        h->d_b = h->d_x = nullptr; h->vec_cap = 0;
+        CUH(cudaMalloc(&h->d_b, vbytes ? vbytes : 8));
+        CUH(cudaMalloc(&h->d_x, vbytes ? vbytes : 8));
+        h->vec_cap = vbytes;
+    }
+    if (nvec > h->flag_cap) {
+        cudaFree(h->d_flags); h->d_flags = nullptr; h->flag_cap = 0;
+        CUH(cudaMalloc(&h->d_flags, sizeof(int) * nvec));
+        h->flag_cap = nvec;
+    }
+    CUH(cudaMemcpyAsync(h->d_b, host_b, vbytes, cudaMemcpyHostToDevice, h->st));
+    int rc = bdilu_solve(h->d_data, h->sys_stride, h->nsys, h->nblocks, h->blockw, h->ndiag, h->nsat, h->ld,
+                         h->d_rowbycol, h->d_colbyrow, h->d_b, h->d_x, nrhs, n, n * nrhs, nullptr, h->d_flags, h->st);
+    if (rc) return rc;
+    CUH(cudaMemcpyAsync(host_x, h->d_x, vbytes, cudaMemcpyDeviceToHost, h->st));
+    int one = 0;
+    int *hf = flags;
+    int *tmp = nullptr;
+    if (!hf) hf = (nvec == 1) ? &one : (tmp = (int *)std::malloc(sizeof(int) * nvec));
+    CUH(cudaMemcpyAsync(hf, h->d_flags, sizeof(int) * nvec, cudaMemcpyDeviceToHost, h->st));
+    CUH(cudaStreamSynchronize(h->st));
+    int first = 0;
+    for (size_t i = 0; i < nvec && !first; ++i) first = hf[i];
+    std::free(tmp);
+    return first;
+}
+
+void bdilu_ilu_destroy(bdilu_ilu *h) { free_handle(h); }
+
+int bdilu_host_dot_vec(const double *host_data, int nblocks, int blockw, int ndiag, int nsat, int ld,
+                       const double *host_vec, double *host_out, int nrhs)
+{
+    if (!host_data || !host_vec || !host_out || nrhs < 1) return set_err(BDILU_ERR_ARG, "null pointer or nrhs < 1");
+    if (bdilu_device_count() < 1) return set_err(BDILU_ERR_CUDA, "no CUDA device: libbdilu_b200 has no CPU fallback");
+    if (ld == 0) ld = bdilu_default_ld(blockw);
+    const int64_t nd = bdilu_ndata(nblocks, blockw, ndiag, nsat, ld), n = (int64_t)nblocks * blockw;
+    double *d_data = nullptr, *d_v = nullptr, *d_o = nullptr;
+    int rc = BDILU_OK;
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_data, sizeof(double) * (nd ? nd : 1))) != cudaSuccess ||
+        (e = cudaMalloc(&d_v, sizeof(double) * (n * nrhs ? n * nrhs : 1))) != cudaSuccess ||
+        (e = cudaMalloc(&d_o, sizeof(double) * (n * nrhs ? n * nrhs : 1))) != cudaSuccess ||
+        (e = cudaMemcpy(d_data, host_data, sizeof(double) * nd, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(d_v, host_vec, sizeof(double) * n * nrhs, cudaMemcpyHostToDevice)) != cudaSuccess) {
+        rc = set_err(BDILU_ERR_CUDA, cudaGetErrorString(e));
+    } else {
+        rc = bdilu_dot_vec(d_data, nd, 1, nblocks, blockw, ndiag, nsat, ld, d_v, d_o, nrhs, n, n * nrhs, nullptr);
+        if (!rc && (e = cudaMemcpy(host_out, d_o, sizeof(double) * n * nrhs, cudaMemcpyDeviceToHost)) != cudaSuccess)
+            rc = set_err(BDILU_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaFree(d_data); cudaFree(d_v); cudaFree(d_o);
+    return rc;
+}
+
+}  // extern "C"
+
+// ---- one-shot ILU(A) + solve(b, x) on host memory, pipelined over slabs of systems ---------------
+namespace {
+struct Workspace {
+    std::mutex mu;
+    double *d_data = nullptr, *d_b = nullptr, *d_x = nullptr;
+    int *d_idx = nullptr, *d_info = nullptr, *d_flags = nullptr;
+    size_t cap_data = 0, cap_vec = 0, cap_x = 0, cap_idx = 0, cap_info = 0, cap_flags = 0;
+    cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+};
+Workspace g_ws;
+
+template <class T>
+cudaError_t grow(T *&p, size_t &cap, size_t want)
+{
+    if (want <= cap) return cudaSuccess;
+    cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+    if (e == cudaSuccess) cap = want;
+    return e;
+}
+}  // namespace
+
+extern "C" int bdilu_host_factor_solve(const double *host_data, int64_t sys_stride, int nsys, int nblocks,
+                                       int blockw, int ndiag, int nsat, int ld, const double *host_b,
+                                       double *host_x, int nrhs, int *info, int *flags)
+{
+    if (!host_data || !host_b || !host_x || nsys < 1 || nrhs < 1)
+        return set_err(BDILU_ERR_ARG, "null pointer, nsys < 1 or nrhs < 1");
+    if (bdilu_device_count() < 1) return set_err(BDILU_ERR_CUDA, "no CUDA device: libbdilu_b200 has no CPU fallback");
+    if (ld == 0) ld = bdilu_default_ld(blockw);
+    const int64_t nd = bdilu_ndata(nblocks, blockw, ndiag, nsat, ld), n = (int64_t)nblocks * blockw;
+    if (nsys == 1) sys_stride = nd;
+    std::lock_guard<std::mutex> lock(g_ws.mu);
+    Workspace &W = g_ws;
+    for (auto &s : W.st)
+        if (!s) CUH(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    // device copy is packed tight (stride nd) whatever the host stride
+    CUH(grow(W.d_data, W.cap_data, (size_t)nsys * nd));
+    CUH(grow(W.d_b, W.cap_vec, (size_t)nsys * nrhs * n));
+    CUH(grow(W.d_x, W.cap_x, (size_t)nsys * nrhs * n));
+    CUH(grow(W.d_idx, W.cap_idx, (size_t)3 * nsys * n));
+    CUH(grow(W.d_info, W.cap_info, (size_t)nsys));
+    CUH(grow(W.d_flags, W.cap_flags, (size_t)nsys * nrhs));
+    int *d_ipiv = W.d_idx, *d_rbc = W.d_idx + (size_t)nsys * n, *d_cbr = W.d_idx + (size_t)2 * nsys * n;
+
+    // slabs of systems round-robin over 3 streams: H2D(slab k+1) overlaps factor+solve(slab k) and D2H(slab k-1)
+    int slab = (nsys + 11) / 12;
+    if (slab < 1) slab = 1;
+    int k = 0;
+    for (int s0 = 0; s0 < nsys; s0 += slab, ++k) {
+        const int ns = (s0 + slab <= nsys) ? slab : nsys - s0;
+        cudaStream_t st = W.st[k % 3];
+        if (sys_stride == nd) {
+            CUH(cudaMemcpyAsync(W.d_data + (size_t)s0 * nd, host_data + (size_t)s0 * nd, sizeof(double) * (size_t)ns * nd,
+                                cudaMemcpyHostToDevice, st));
+        } else {
+            CUH(cudaMemcpy2DAsync(W.d_data + (size_t)s0 * nd, sizeof(double) * nd, host_data + (size_t)s0 * sys_stride,
+                                  sizeof(double) * sys_stride, sizeof(double) * nd, ns, cudaMemcpyHostToDevice, st));
+        }
+        CUH(cudaMemcpyAsync(W.d_b + (size_t)s0 * nrhs * n, host_b + (size_t)s0 * nrhs * n,
+                            sizeof(double) * (size_t)ns * nrhs * n, cudaMemcpyHostToDevice, st));
+        int rc = bdilu_factor_solve(W.d_data + (size_t)s0 * nd, nd, ns, nblocks, blockw, ndiag, nsat, ld,
+                                    d_ipiv + (size_t)s0 * n, d_rbc + (size_t)s0 * n, d_cbr + (size_t)s0 * n,
+                                    W.d_info + s0, W.d_b + (size_t)s0 * nrhs * n, W.d_x + (size_t)s0 * nrhs * n, nrhs, n,
+                                    n * nrhs, W.d_flags + (size_t)s0 * nrhs, st);
+        if (rc) return rc;
+        CUH(cudaMemcpyAsync(host_x + (size_t)s0 * nrhs * n, W.d_x + (size_t)s0 * nrhs * n,
+                            sizeof(double) * (size_t)ns * nrhs * n, cudaMemcpyDeviceToHost, st));
+        if (info) CUH(cudaMemcpyAsync(info + s0, W.d_info + s0, sizeof(int) * ns, cudaMemcpyDeviceToHost, st));
+        if (flags)
+            CUH(cudaMemcpyAsync(flags + (size_t)s0 * nrhs, W.d_flags + (size_t)s0 * nrhs, sizeof(int) * (size_t)ns * nrhs,
+                                cudaMemcpyDeviceToHost, st));
+    }
+    for (auto &s : W.st) CUH(cudaStreamSynchronize(s));
+    return BDILU_OK;
+}

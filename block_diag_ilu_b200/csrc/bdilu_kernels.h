@@ -1,0 +1,36 @@
+// Internal launch interface between the C ABI (bdilu_capi.cu) and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bdilu_common.cuh"
+
+namespace bdilu {
+
+void count_launch(int n);
+void set_last_error(const char *msg);  // feeds bdilu_last_error() on the calling thread
+
+// strides of right-hand-side / solution vectors (in doubles)
+struct VecLayout {
+    int nrhs;
+    int64_t rhs_stride, sys_stride;
+};
+
+cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
+                          int *rowbycol, int *colbyrow, int *info, cudaStream_t st);
+
+cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                         const int *rowbycol, const int *colbyrow, const double *b, double *x,
+                         const VecLayout &V, int *flags, cudaStream_t st);
+
+cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                           const double *vec, double *out, const VecLayout &V, cudaStream_t st);
+
+cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                                  const double *b, const double *x, const VecLayout &V, double *norm2,
+                                  cudaStream_t st);
+
+cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int nsys,
+                                  const Dims &D, double scale, double diag_add, cudaStream_t st);
+
+}  // namespace bdilu

@@ -1,0 +1,132 @@
+// Kernel 3: BlockDiagMatrix<double>::dot_vec (block_diag_ilu.hpp:295-326), the residual b - A x and
+// its squared 2-norm per (system, vector), plus scale_diag_add (:276-287).
+//
+// Purely streaming: every matrix element is read once.  One thread per output row; consecutive
+// threads read consecutive rows of a column-major block column, so each column load is one
+// contiguous 8*blockw-byte segment.  The reference scatters sub/sup/top/bot contributions into
+// `out`; here each row gathers the (at most 2*ndiag + satellite) couplings that land on it, so no
+// zero-fill pass and no atomics are needed.
+#include "bdilu_common.cuh"
+#include "bdilu_kernels.h"
+
+namespace bdilu {
+
+constexpr int MV_THREADS = 128;
+
+__device__ __forceinline__ double row_dot(const double *__restrict__ sd, const Dims &D,
+                                          const double *__restrict__ vec, int bi, int row)
+{
+    const int w = D.w, N = D.nblocks;
+    const double *col = sd + D.block(bi) + row;
+    const double *v = vec + bi * w;
+    double acc = 0.0;
+#pragma unroll 8
+    for (int c = 0; c < w; ++c) acc = fma(ld_stream(col + (int64_t)c * D.ld), __ldg(v + c), acc);
+    for (int di = 0; di < D.ndiag; ++di) {
+        if (bi + di + 1 < N)  // sup(di,bi,row) sits at (bi*w+row, (bi+di+1)*w+row)
+            acc = fma(ld_stream(sd + D.off_sup + D.diag_chunk(di, bi) + row), __ldg(vec + (bi + di + 1) * w + row), acc);
+        if (bi - di - 1 >= 0)  // sub(di,bi-di-1,row) sits at (bi*w+row, (bi-di-1)*w+row)
+            acc = fma(ld_stream(sd + D.off_sub + D.diag_chunk(di, bi - di - 1) + row), __ldg(vec + (bi - di - 1) * w + row), acc);
+    }
+    for (int sati = 0; sati < D.nsat; ++sati) {
+        if (bi <= sati)  // top(sati,bi,row) sits at (bi*w+row, (N-1-sati+bi)*w+row)
+            acc = fma(ld_stream(sd + D.off_top + D.sat_chunk(sati, bi) + row), __ldg(vec + (N - 1 - sati + bi) * w + row), acc);
+        const int bj = bi - N + 1 + sati;  // bot(sati,bj,row) sits at ((N-1-sati+bj)*w+row, bj*w+row)
+        if (bj >= 0)
+            acc = fma(ld_stream(sd + D.off_bot + D.sat_chunk(sati, bj) + row), __ldg(vec + bj * w + row), acc);
+    }
+    return acc;
+}
+
+// MODE 0: out = A*vec.  MODE 1: norm2 += sum (b - A*x)^2 (vec = x, rhsb = b).
+template <int MODE>
+__global__ void __launch_bounds__(MV_THREADS)
+matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const double *__restrict__ vec,
+              const double *__restrict__ rhsb, double *__restrict__ out, VecLayout V)
+{
+    const int sys = blockIdx.z, rhs = blockIdx.y;
+    const int n = D.nblocks * D.w;
+    const int i = blockIdx.x * MV_THREADS + threadIdx.x;
+    const double *sd = data + (int64_t)sys * sys_stride;
+    const int64_t voff = (int64_t)sys * V.sys_stride + (int64_t)rhs * V.rhs_stride;
+    double val = 0.0;
+    if (i < n) {
+        const int bi = i / D.w, row = i - bi * D.w;
+        val = row_dot(sd, D, vec + voff, bi, row);
+        if (MODE == 0) out[voff + i] = val;
+        else { val = __ldg(rhsb + voff + i) - val; val *= val; }
+    }
+    if (MODE == 1) {
+        __shared__ double part[MV_THREADS / 32];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) val += group_bcast<32>(val, (threadIdx.x & 31) ^ off);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = val;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+            for (int k = 0; k < MV_THREADS / 32; ++k) s += part[k];
+            atomicAdd(out + (int64_t)sys * V.nrhs + rhs, s);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+scale_diag_add_kernel(double *__restrict__ dst, const double *__restrict__ src, int64_t sys_stride, Dims D,
+                      double scale, double diag_add)
+{
+    const int sys = blockIdx.y;
+    const int64_t base = (int64_t)sys * sys_stride;
+    const int64_t blk_end = D.off_sub;
+    const int64_t per_block = (int64_t)D.w * D.ld;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D.ndata;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        double v = scale * src[base + i];
+        if (i < blk_end) {
+            const int64_t in_blk = i % per_block;
+            const int c = (int)(in_blk / D.ld), r = (int)(in_blk % D.ld);
+            if (r == c) v += diag_add;
+        }
+        dst[base + i] = v;
+    }
+}
+
+cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                           const double *vec, double *out, const VecLayout &V, cudaStream_t st)
+{
+    const int n = D.nblocks * D.w;
+    if (n == 0 || nsys == 0 || V.nrhs == 0) return cudaSuccess;
+    if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
+    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, V.nrhs, nsys);
+    matvec_kernel<0><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                                  const double *b, const double *x, const VecLayout &V, double *norm2,
+                                  cudaStream_t st)
+{
+    const int n = D.nblocks * D.w;
+    if (nsys == 0 || V.nrhs == 0) return cudaSuccess;
+    if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
+    if (e != cudaSuccess || n == 0) return e;
+    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, V.nrhs, nsys);
+    matvec_kernel<1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int nsys,
+                                  const Dims &D, double scale, double diag_add, cudaStream_t st)
+{
+    if (nsys == 0 || D.ndata == 0) return cudaSuccess;
+    if (nsys > 65535) return cudaErrorInvalidValue;
+    const int64_t want = (D.ndata + 255) / 256;
+    dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), nsys);
+    scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst, src, sys_stride, D, scale, diag_add);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+}  // namespace bdilu
