@@ -98,6 +98,13 @@ int64_t bdilu_ndata(int nblocks, int blockw, int ndiag, int nsat, int ld)
     return make_dims(nblocks, blockw, ndiag, nsat, ld).ndata;
 }
 
+int bdilu_debug_force_chain_solve(int on)
+{
+    const int old = g_force_chain ? 1 : 0;
+    g_force_chain = on != 0;
+    return old;
+}
+
 int64_t bdilu_launch_count(void) { return g_launches.load(); }
 void bdilu_launch_count_reset(void) { g_launches.store(0); }
 

@@ -23,6 +23,11 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
+extern bool g_force_chain;
+bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
+                           const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
+                           cudaStream_t st, cudaError_t *err);
+
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st);
 

@@ -155,6 +155,10 @@ BDILU_API int bdilu_host_factor_solve(const double *host_data, int64_t sys_strid
                             int nblocks, int blockw, int ndiag, int nsat, int ld,
                             const double *host_b, double *host_x, int nrhs, int *info, int *flags);
 
+/* Test hook: nonzero forces bdilu_solve onto the general chain kernel even where the wavefront kernel
+ * applies (both paths are parity-tested).  Returns the previous setting. */
+BDILU_API int bdilu_debug_force_chain_solve(int on);
+
 /* Kernels launched by this library since load / last reset (bench.py's gpu_launches claim). */
 BDILU_API int64_t bdilu_launch_count(void);
 BDILU_API void bdilu_launch_count_reset(void);

@@ -91,9 +91,25 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-def test_config3_shape_subset(oracle):
+@pytest.fixture(params=["wave", "chain"])
+def solve_path(request):
+    """Run the case on the wavefront solve kernel (default where it applies) and on the general chain kernel."""
+    from block_diag_ilu_b200 import _lib
+    old = _lib.lib().bdilu_debug_force_chain_solve(1 if request.param == "chain" else 0)
+    yield request.param
+    _lib.lib().bdilu_debug_force_chain_solve(old)
+
+
+def test_config3_shape_subset(oracle, solve_path):
     run_case(oracle, 2, 8192, 32, 2, "D")
     run_case(oracle, 1, 2048, 32, 2, "P", seed0=77, yardstick=True)
+
+
+@pytest.mark.parametrize("N,w,d,ld", [(64, 32, 1, 32), (200, 32, 2, 32), (333, 32, 3, 34), (100, 16, 1, 16),
+                                      (129, 8, 2, 8), (77, 24, 4, 24), (640, 4, 1, 4), (90, 20, 2, 22)])
+@pytest.mark.parametrize("fam", ["D", "P"])
+def test_wavefront_shapes(oracle, solve_path, N, w, d, ld, fam):
+    run_case(oracle, 2, N, w, d, fam, ld=ld, nrhs=3, yardstick=(fam == "P"))
 
 
 def test_config4_shape(oracle):
