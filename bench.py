@@ -308,10 +308,11 @@ def run_ours(args, rank, world, local_rank):
             e2e_call()
         t_e2e = (time.perf_counter() - t0) / e2e_steps
         assert not h_info.any() and not h_flags.any()
-        assert float((h_x.to(device) - x).abs().max().item()) == 0.0
+        e2e_diff = float((h_x.to(device) - x).abs().max().item())
+        assert e2e_diff <= 1e-12 * float(x.abs().max().item()), "host-pointer path disagrees with the device path"
         line["e2e"] = {"value": nsys * N / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h_data.numel() * 8 + h_b.numel() * 8),
                        "d2h_bytes_per_step": int(h_x.numel() * 8 + 4 * nsys + 4 * nsys * nrhs), "ms_per_step": 1e3 * t_e2e,
-                       "steps": e2e_steps, "n_gpus": 1,
+                       "steps": e2e_steps, "n_gpus": 1, "bit_identical_to_device_path": e2e_diff == 0.0,
                        "api": "bdilu_host_factor_solve (host-pointer C ABI; pinned host buffers; slabs pipelined over 3 streams)"}
     sampler.stop_flag = True
     sampler.join(timeout=1.0)

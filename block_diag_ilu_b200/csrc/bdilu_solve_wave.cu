@@ -221,25 +221,36 @@ __device__ void consume(const Args &A, const Smem &S, int it0, int j, int r, int
         const double rinv = 1.0 / dg;
         double *myslot = S.ring + (i % (2 * NW)) * 32;
 
+        // Coupling terms are summed into `cacc` in a FIXED order (farthest sub-diagonal first, i.e. the
+        // order the values become available) and subtracted from the row at a FIXED step (just before the
+        // row's last L/U term), so the rounding does not depend on when the values happen to arrive:
+        // results are bit-reproducible from run to run.
+        double cacc = 0.0;
         auto poll = [&]() {
+            bool go = true;
 #pragma unroll
-            for (int d = 0; d < MAXD; ++d) {
-                if (need & (1u << d)) {
+            for (int d = MAXD - 1; d >= 0; --d) {
+                if (go && (need & (1u << d))) {
                     const double v = ld_volatile_s(&S.ring[((i - 1 - d) % (2 * NW)) * 32 + ci]);
                     if (!is_sent(v)) {
-                        acc = fma(-cv[d], v, acc);
+                        cacc = fma(cv[d], v, cacc);
                         need &= ~(1u << d);
+                    } else {
+                        go = false;
                     }
                 }
             }
         };
+        const int kapply = FWD ? max(r - 1, 0) : min(r + 1, w - 1);
 
 #pragma unroll 4
         for (int kk = 0; kk < w; ++kk) {
             const int k = FWD ? kk : w - 1 - kk;
             const double lk = (rowok && (FWD ? r > k : r < k)) ? Ls[k * ld + r] : 0.0;
             if (need) poll();
-            while (__any_sync(FULL, r == k && need != 0)) poll();
+            const bool apply_now = rowok && k == kapply;
+            while (__any_sync(FULL, apply_now && need != 0)) poll();
+            if (apply_now) acc -= cacc;
             if (!FWD && r == k) {
                 // x = acc / U[k][k]: reciprocal + one Newton correction gives the correctly rounded
                 // quotient off the slow division path; a zero diagonal takes the true division so that
