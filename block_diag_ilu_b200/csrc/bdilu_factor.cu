@@ -52,20 +52,181 @@ __device__ __forceinline__ int group_argmax(double v, int pos, int r)
     }
 }
 
+// ---- lean path -------------------------------------------------------------------------------------
+// Straight-line elimination step: no branch inside the 32-step unrolled loop, so ptxas can overlap the
+// pivot search of step k+1 (it only needs column k+1) with the trailing update of step k.
+//   * pivot search on integer keys: |a| as (hi & 0x7fffffff, lo); three warp reductions give
+//     max hi -> max lo among those -> min position among those (idamax: first maximum);
+//   * every candidate lane computes 1/a[k] speculatively while the search runs; the winner publishes
+//     it next to its row, and l = a/piv is formed as q = a*rinv; q += (a - q*piv)*rinv, which is the
+//     correctly rounded quotient when rinv is the correctly rounded reciprocal (Markstein) -- the same
+//     value the reference's true division gives (tests/test_block_diag.cpp:139-142 check exact quotients);
+//   * rows that are already pivot rows, and steps with an exactly zero pivot (dgetf2 leaves that column
+//     unscaled and records info), use l = 0 instead of a branch.
+// Pivots outside the range where the branch-free reciprocal is exact (|x| < 2^-990 or > 2^990, inf, NaN)
+// set `weird`; such a warp redoes its block on the slow true-division path below before storing anything.
+
+// 1/x for normal-range x: MUFU.RCP64H seed + the refinement CUDA's own IEEE reciprocal uses on its fast path.
+__device__ __forceinline__ double rcp_fast(double x)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    e = fma(e, e, e);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+
+template <int G>
+__device__ __forceinline__ int group_max_i(int v)
+{
+    if (G == 32) return __reduce_max_sync(FULL, v);
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) v = max(v, __shfl_xor_sync(FULL, v, off, G));
+    return v;
+}
+template <int G>
+__device__ __forceinline__ unsigned group_max_u(unsigned v)
+{
+    if (G == 32) return __reduce_max_sync(FULL, v);
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) v = max(v, __shfl_xor_sync(FULL, v, off, G));
+    return v;
+}
+template <int G>
+__device__ __forceinline__ unsigned group_min_u(unsigned v)
+{
+    if (G == 32) return __reduce_min_sync(FULL, v);
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) v = min(v, __shfl_xor_sync(FULL, v, off, G));
+    return v;
+}
+
+// Slow path (true divisions, branches): the algorithm exactly as documented at the top of this file.
+// Also the only path for 32 < blockw (see factor_wide_kernel).  a[] holds the unfactored row on entry.
+struct RowState {
+    int pos, ipiv, info;
+    double diag;
+};
+
+// Stores what one lane owns after the elimination: its row of L\U at row `pos`, the permutation
+// vectors, the scaled sub/bot entries of column r, and the block's info.
 template <int WP>
-__global__ void __launch_bounds__(FACTOR_WARPS * 32)
+__device__ __forceinline__ void store_block(const double (&a)[WP], const RowState &S, double *sysdata, double *blk,
+                                            const Dims &D, int w, int ld, int sys, int bi, int r,
+                                            int *__restrict__ ipiv, int *__restrict__ rowbycol,
+                                            int *__restrict__ colbyrow, int *__restrict__ info)
+{
+#pragma unroll
+    for (int c = 0; c < WP; ++c)
+        if (c < w) blk[(int64_t)c * ld + S.pos] = a[c];
+    const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
+    ipiv[ib + r] = S.ipiv;
+    rowbycol[ib + S.pos] = r;
+    colbyrow[ib + r] = S.pos;
+    // sub(di,bi,c) /= U[c][c]  (block_diag_ilu.hpp:471-475)
+    for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
+        double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
+        *s = *s / S.diag;
+    }
+    // bot(sati,bi,c) /= U[c][c]  (:476-479)
+    if (bi < D.nsat)
+        for (int sati = bi; sati < D.nsat; ++sati) {
+            double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
+            *s = *s / S.diag;
+        }
+    if (S.info != 0 && r == 0) {
+        // keep the failing block with the lowest index (serial loop order, :469-470)
+        const int key = (bi << 7) | S.info;
+        int old = atomicCAS(&info[sys], 0, key);
+        while (old != 0 && (old >> 7) > bi) {
+            const int assumed = old;
+            old = atomicCAS(&info[sys], assumed, key);
+            if (old == assumed) break;
+        }
+    }
+}
+
+// Slow path (true divisions, branches, rows in local memory): the algorithm exactly as documented at the
+// top of this file, from the pristine block in global memory.  Taken only by warps that met a pivot
+// outside the fast reciprocal's exact range.
+template <int WP>
+__device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dims D, int w, int ld, int sys, int bi,
+                                               int r, bool live, double *ubuf, int *__restrict__ ipiv,
+                                               int *__restrict__ rowbycol, int *__restrict__ colbyrow,
+                                               int *__restrict__ info)
+{
+    constexpr int G = WP;
+    const bool rowok = r < w;
+    double a[WP];
+    for (int c = 0; c < WP; ++c)
+        a[c] = (rowok && c < w) ? blk[(int64_t)c * ld + r] : ((c == r) ? 1.0 : 0.0);
+    RowState S;
+    S.pos = r; S.ipiv = r + 1; S.info = 0; S.diag = 1.0;
+    bool active = rowok;
+    for (int k = 0; k < w; ++k) {
+        const double v = active ? fabs(a[k]) : -1.0;
+        const int p = group_argmax<G>(v, S.pos, r);
+        const int q = __shfl_sync(FULL, S.pos, p, G);
+        if (r == k) S.ipiv = q + 1;
+        if (S.pos == k) S.pos = q;
+        if (r == p) { S.pos = k; active = false; }
+        __syncwarp();
+        if (r == p)
+            for (int c = k; c < WP; ++c) ubuf[c] = a[c];
+        __syncwarp();
+        const double piv = ubuf[k];
+        if (r == k) S.diag = piv;
+        if (piv == 0.0) {
+            if (S.info == 0) S.info = k + 1;
+        } else if (active) {
+            const double l = a[k] / piv;
+            a[k] = l;
+            for (int c = k + 1; c < WP; ++c) a[c] = fma(-l, ubuf[c], a[c]);
+        }
+    }
+    if (live && rowok) {
+        for (int c = 0; c < w; ++c) blk[(int64_t)c * ld + S.pos] = a[c];
+        const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
+        ipiv[ib + r] = S.ipiv;
+        rowbycol[ib + S.pos] = r;
+        colbyrow[ib + r] = S.pos;
+        for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
+            double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
+            *s = *s / S.diag;
+        }
+        if (bi < D.nsat)
+            for (int sati = bi; sati < D.nsat; ++sati) {
+                double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
+                *s = *s / S.diag;
+            }
+        if (S.info != 0 && r == 0) {
+            const int key = (bi << 7) | S.info;
+            int old = atomicCAS(&info[sys], 0, key);
+            while (old != 0 && (old >> 7) > bi) {
+                const int assumed = old;
+                old = atomicCAS(&info[sys], assumed, key);
+                if (old == assumed) break;
+            }
+        }
+    }
+}
+
+template <int WP, bool EXACT>
+__global__ void __launch_bounds__(FACTOR_WARPS * 32, WP == 32 ? 4 : 6)
 factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
               int *__restrict__ ipiv, int *__restrict__ rowbycol, int *__restrict__ colbyrow,
               int *__restrict__ info)
 {
     constexpr int G = WP;
     constexpr int BPW = 32 / G;
-    // pivot-row mailbox: [warp][group][2 buffers][WP]
-    __shared__ __align__(16) double urow_s[FACTOR_WARPS][BPW][2][WP];
+    // pivot-row mailbox: [warp][group][2 buffers][WP doubles + reciprocal of the pivot (+ pad)]
+    __shared__ __align__(16) double urow_s[FACTOR_WARPS][BPW][2][WP + 2];
 
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const int grp = lane / G, r = lane % G;
-    const int w = D.w, ld = D.ld;
+    const int w = EXACT ? WP : D.w, ld = D.ld;
     const int64_t total = (int64_t)nsys * D.nblocks;
     int64_t gb = ((int64_t)blockIdx.x * FACTOR_WARPS + wic) * BPW + grp;
     const bool live = gb < total;  // dead groups run on the last block but store nothing
@@ -75,86 +236,80 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     double *blk = sysdata + D.block(bi);
     const bool rowok = r < w;
 
-    // row r of the block; rows/columns beyond w are padded with the identity
+    // row r of the block; rows/columns beyond w are padded with the identity (they pivot on themselves
+    // in the trailing steps k >= w and never disturb the real rows)
     double a[WP];
 #pragma unroll
     for (int c = 0; c < WP; ++c)
         a[c] = (rowok && c < w) ? ld_stream(blk + (int64_t)c * ld + r) : ((c == r) ? 1.0 : 0.0);
 
-    double (*urow)[WP] = urow_s[wic][grp];
+    double (*urow)[WP + 2] = urow_s[wic][grp];
     int pos = r;          // current position of my row in the swapped ordering
-    bool active = rowok;  // not yet chosen as a pivot row
+    bool active = true;   // not yet chosen as a pivot row (padded rows take part: see above)
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
     double my_diag = 1.0; // lane k keeps U[k][k]
     int my_info = 0;
+    bool weird = false;
 
 #pragma unroll
     for (int k = 0; k < WP; ++k) {
-        if (k < w) {
-            const double v = active ? fabs(a[k]) : -1.0;
-            const int p = group_argmax<G>(v, pos, r);
-            const int q = __shfl_sync(FULL, pos, p, G);
-            if (r == k) my_ipiv = q + 1;
-            if (pos == k) pos = q;
-            if (r == p) { pos = k; active = false; }
+        // ---- pivot search (idamax over the not-yet-chosen rows, ties -> lowest current position) ----
+        const int hi = active ? (__double2hiint(a[k]) & 0x7fffffff) : -1;
+        const unsigned lo = (unsigned)__double2loint(a[k]);
+        const double myrcp = rcp_fast(a[k]);  // speculative; only the winner's is used
+        const int mhi = group_max_i<G>(hi);
+        const bool c1 = (hi == mhi);
+        const unsigned mlo = group_max_u<G>(c1 ? lo : 0u);
+        const bool c2 = c1 && (lo == mlo);
+        const unsigned q = group_min_u<G>(c2 ? (unsigned)pos : 0xffffu);  // position of the chosen row
+        const bool is_p = c2 && ((unsigned)pos == q);
+        if (r == k) my_ipiv = (int)q + 1;
+        if (pos == k) pos = (int)q;
+        if (is_p) { pos = k; active = false; }
 
-            // publish the pivot row (columns k..WP-1) to the group
-            double2 *u2w = reinterpret_cast<double2 *>(urow[k & 1]);
-            if (r == p) {
+        // ---- publish the pivot row (columns k..WP-1) and 1/pivot to the group ----
+        double *ub = urow[k & 1];
+        if (is_p) {
+            double2 *u2w = reinterpret_cast<double2 *>(ub);
 #pragma unroll
-                for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
-            }
-            __syncwarp();
-            const double2 *u2 = reinterpret_cast<const double2 *>(urow[k & 1]);
-            double u[WP];
-#pragma unroll
-            for (int m = k / 2; m < WP / 2; ++m) {
-                const double2 t = u2[m];
-                u[2 * m] = t.x;
-                u[2 * m + 1] = t.y;
-            }
-            const double piv = u[k];
-            if (r == k) my_diag = piv;
-            if (piv == 0.0) {
-                if (my_info == 0) my_info = k + 1;  // dgetf2: record, leave the column unscaled
-            } else if (active) {
-                const double l = a[k] / piv;  // true division: the reference tests exact quotients
-                a[k] = l;
-#pragma unroll
-                for (int j = k + 1; j < WP; ++j) a[j] = fma(-l, u[j], a[j]);
-            }
+            for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
+            ub[WP] = myrcp;
         }
+        __syncwarp();
+        const double2 *u2 = reinterpret_cast<const double2 *>(ub);
+        double u[WP];
+#pragma unroll
+        for (int m = k / 2; m < WP / 2; ++m) {
+            const double2 t = u2[m];
+            u[2 * m] = t.x;
+            u[2 * m + 1] = t.y;
+        }
+        const double piv = u[k], rinv = ub[WP];
+        const int ehi = (__double2hiint(piv) >> 20) & 0x7ff;
+        const bool nz = (piv != 0.0);
+        weird |= nz && (ehi < 0x020 || ehi > 0x7dd);
+        if (r == k) my_diag = piv;
+        if (!nz && my_info == 0) my_info = k + 1;  // dgetf2: record, leave the column unscaled
+
+        // ---- multiplier by (exactly rounded) division, rank-1 update of the trailing columns ----
+        double l = a[k] * rinv;
+        l = fma(fma(-l, piv, a[k]), rinv, l);
+        const bool upd = active && nz;
+        a[k] = upd ? l : a[k];
+        l = upd ? l : 0.0;
+#pragma unroll
+        for (int j = k + 1; j < WP; ++j) a[j] = fma(-l, u[j], a[j]);
     }
 
+    if (__any_sync(FULL, weird)) {
+        // rare: redo this warp's blocks with true divisions from the pristine data (nothing stored yet)
+        factor_block_slow<WP>(sysdata, blk, D, w, ld, sys, bi, r, live, urow[0], ipiv, rowbycol, colbyrow, info);
+        return;
+    }
     if (live && rowok) {
-#pragma unroll
-        for (int c = 0; c < WP; ++c)
-            if (c < w) blk[(int64_t)c * ld + pos] = a[c];
-        const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
-        ipiv[ib + r] = my_ipiv;
-        rowbycol[ib + pos] = r;
-        colbyrow[ib + r] = pos;
-        // sub(di,bi,c) /= U[c][c]  (block_diag_ilu.hpp:471-475)
-        for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
-            double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
-            *s = *s / my_diag;
-        }
-        // bot(sati,bi,c) /= U[c][c]  (:476-479)
-        if (bi < D.nsat)
-            for (int sati = bi; sati < D.nsat; ++sati) {
-                double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
-                *s = *s / my_diag;
-            }
-        if (my_info != 0 && r == 0) {
-            // keep the failing block with the lowest index (serial loop order, :469-470)
-            const int key = (bi << 7) | my_info;
-            int old = atomicCAS(&info[sys], 0, key);
-            while (old != 0 && (old >> 7) > bi) {
-                const int assumed = old;
-                old = atomicCAS(&info[sys], assumed, key);
-                if (old == assumed) break;
-            }
-        }
+        RowState S;
+        S.pos = pos; S.ipiv = my_ipiv; S.info = my_info; S.diag = my_diag;
+        store_block<WP>(a, S, sysdata, blk, D, w, ld, sys, bi, r, ipiv, rowbycol, colbyrow, info);
     }
 }
 
@@ -270,8 +425,12 @@ cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims
     {                                                                                              \
         const int64_t per_cta = (int64_t)FACTOR_WARPS * (32 / WP);                                 \
         const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);                         \
-        factor_kernel<WP><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv,     \
-                                                              rowbycol, colbyrow, info);           \
+        if (D.w == WP)                                                                             \
+            factor_kernel<WP, true><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, \
+                                                                        rowbycol, colbyrow, info);  \
+        else                                                                                       \
+            factor_kernel<WP, false><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, \
+                                                                         rowbycol, colbyrow, info); \
     }
     const int w = D.w;
     if (w <= 2) BDILU_LAUNCH_FACTOR(2)
