@@ -100,8 +100,8 @@ int64_t bdilu_ndata(int nblocks, int blockw, int ndiag, int nsat, int ld)
 
 int bdilu_debug_force_chain_solve(int on)
 {
-    const int old = g_force_chain ? 1 : 0;
-    g_force_chain = on != 0;
+    const int old = g_solve_path;
+    g_solve_path = on;
     return old;
 }
 

@@ -46,4 +46,24 @@ __device__ __forceinline__ double ld_stream(const double *p)
     return __ldcs(p);
 }
 
+// 1/x for normal-range x: MUFU.RCP64H seed + the refinement CUDA's own IEEE reciprocal uses on its fast
+// path (correctly rounded for |x| in [2^-990, 2^990]; callers test the exponent and take a true division
+// otherwise).
+__device__ __forceinline__ double rcp_fast(double x)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    e = fma(e, e, e);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+// true when the exponent of x is inside the range where rcp_fast is exact
+__device__ __forceinline__ bool rcp_fast_ok(double x)
+{
+    const int ehi = (__double2hiint(x) >> 20) & 0x7ff;
+    return ehi >= 0x020 && ehi <= 0x7dd;
+}
+
 }  // namespace bdilu

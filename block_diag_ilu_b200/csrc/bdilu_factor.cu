@@ -66,18 +66,6 @@ __device__ __forceinline__ int group_argmax(double v, int pos, int r)
 // Pivots outside the range where the branch-free reciprocal is exact (|x| < 2^-990 or > 2^990, inf, NaN)
 // set `weird`; such a warp redoes its block on the slow true-division path below before storing anything.
 
-// 1/x for normal-range x: MUFU.RCP64H seed + the refinement CUDA's own IEEE reciprocal uses on its fast path.
-__device__ __forceinline__ double rcp_fast(double x)
-{
-    double y;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    double e = fma(-x, y, 1.0);
-    e = fma(e, e, e);
-    y = fma(y, e, y);
-    e = fma(-x, y, 1.0);
-    return fma(y, e, y);
-}
-
 template <int G>
 __device__ __forceinline__ int group_max_i(int v)
 {

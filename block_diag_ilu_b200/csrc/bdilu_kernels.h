@@ -23,10 +23,14 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
-extern bool g_force_chain;
+extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel
 bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                            cudaStream_t st, cudaError_t *err);
+
+cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double *data, int64_t sys_stride, const Dims &D,
+                                const int *rowbycol, const int *colbyrow, const double *b, double *x,
+                                const VecLayout &V, int *flags, cudaStream_t st);
 
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st);

@@ -204,7 +204,7 @@ solve_chain_kernel(const double *__restrict__ data, int64_t sys_stride, int nsys
         flags[gid] = (nan_first != 0x7fffffff) ? nan_first : (zero_last >= 0 ? N * w + zero_last : 0);
 }
 
-bool g_force_chain = false;  // test hook: bdilu_debug_force_chain_solve()
+int g_solve_path = 0;  // test hook: bdilu_debug_force_chain_solve()
 
 cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
@@ -213,7 +213,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
     const int64_t total = (int64_t)nsys * V.nrhs;
     if (total == 0 || D.nblocks == 0) return cudaSuccess;
     cudaError_t werr;
-    if (!g_force_chain && try_launch_solve_wave(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr))
+    if (g_solve_path != 1 && try_launch_solve_wave(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr))
         return werr;
 #define BDILU_LAUNCH_SOLVE(WP)                                                                       \
     {                                                                                                \

@@ -155,8 +155,9 @@ BDILU_API int bdilu_host_factor_solve(const double *host_data, int64_t sys_strid
                             int nblocks, int blockw, int ndiag, int nsat, int ld,
                             const double *host_b, double *host_x, int nrhs, int *info, int *flags);
 
-/* Test hook: nonzero forces bdilu_solve onto the general chain kernel even where the wavefront kernel
- * applies (both paths are parity-tested).  Returns the previous setting. */
+/* Test hook: 1 forces bdilu_solve onto the general chain kernel, 2 onto the generic wavefront kernel,
+ * even where a faster kernel applies (every path is parity-tested); 0 = automatic.  Returns the
+ * previous setting. */
 BDILU_API int bdilu_debug_force_chain_solve(int on);
 
 /* Kernels launched by this library since load / last reset (bench.py's gpu_launches claim). */

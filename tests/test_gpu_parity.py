@@ -91,11 +91,12 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-@pytest.fixture(params=["wave", "chain"])
+@pytest.fixture(params=["auto", "chain", "wave_generic"])
 def solve_path(request):
-    """Run the case on the wavefront solve kernel (default where it applies) and on the general chain kernel."""
+    """Run the case on the automatically chosen solve kernel (wave32 / generic wavefront where they apply),
+    on the general chain kernel, and on the generic wavefront kernel."""
     from block_diag_ilu_b200 import _lib
-    old = _lib.lib().bdilu_debug_force_chain_solve(1 if request.param == "chain" else 0)
+    old = _lib.lib().bdilu_debug_force_chain_solve({"auto": 0, "chain": 1, "wave_generic": 2}[request.param])
     yield request.param
     _lib.lib().bdilu_debug_force_chain_solve(old)
 
