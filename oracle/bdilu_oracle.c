@@ -9,7 +9,7 @@
  *   (1) every known-answer vector the reference's own tests hold for the path
  *       (tests/golden/reference_kats.py, transcribed with file:line citations), and
  *   (2) outputs of the untouched reference header compiled in place (oracle/_ref/, see
- *       oracle/Makefile) on seeded random inputs, committed as tests/golden/ref_*.npz.
+ *       oracle/build_oracle.py) on seeded random inputs, committed as tests/golden/ref_vectors.npz.
  *
  * Each function cites the reference lines it restates (paths relative to /root/reference).
  * The per-block LU in the reference is LAPACK dgetrf (third-party, not vendored, not version
