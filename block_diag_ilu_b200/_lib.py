@@ -30,6 +30,7 @@ _SIGNATURES = {
     "bdilu_ilu_solve": (_i, [_p, _p, _p, _i, _p]),
     "bdilu_ilu_destroy": (None, [_p]),
     "bdilu_host_dot_vec": (_i, [_p] + _DIMS + [_p, _p, _i]),
+    "bdilu_host_scale_diag_add": (_i, [_p, _p] + _DIMS + [_d, _d]),
     "bdilu_host_factor_solve": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _p, _p]),
     "bdilu_debug_force_chain_solve": (_i, [_i]),
     "bdilu_launch_count": (_i64, []),

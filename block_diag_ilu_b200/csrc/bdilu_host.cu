@@ -166,6 +166,28 @@ int bdilu_host_dot_vec(const double *host_data, int nblocks, int blockw, int ndi
     return rc;
 }
 
+int bdilu_host_scale_diag_add(double *host_dst, const double *host_src, int nblocks, int blockw, int ndiag, int nsat,
+                              int ld, double scale, double diag_add)
+{
+    if (!host_dst || !host_src) return set_err(BDILU_ERR_ARG, "null pointer");
+    if (bdilu_device_count() < 1) return set_err(BDILU_ERR_CUDA, "no CUDA device: libbdilu_b200 has no CPU fallback");
+    if (ld == 0) ld = bdilu_default_ld(blockw);
+    const int64_t nd = bdilu_ndata(nblocks, blockw, ndiag, nsat, ld);
+    double *d = nullptr;
+    int rc = BDILU_OK;
+    cudaError_t e;
+    if ((e = cudaMalloc(&d, sizeof(double) * (nd ? nd : 1))) != cudaSuccess ||
+        (e = cudaMemcpy(d, host_src, sizeof(double) * nd, cudaMemcpyHostToDevice)) != cudaSuccess) {
+        rc = set_err(BDILU_ERR_CUDA, cudaGetErrorString(e));
+    } else {
+        rc = bdilu_scale_diag_add(d, d, nd, 1, nblocks, blockw, ndiag, nsat, ld, scale, diag_add, nullptr);
+        if (!rc && (e = cudaMemcpy(host_dst, d, sizeof(double) * nd, cudaMemcpyDeviceToHost)) != cudaSuccess)
+            rc = set_err(BDILU_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaFree(d);
+    return rc;
+}
+
 }  // extern "C"
 
 // ---- one-shot ILU(A) + solve(b, x) on host memory, pipelined over slabs of systems ---------------

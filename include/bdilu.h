@@ -149,6 +149,11 @@ BDILU_API void bdilu_ilu_destroy(bdilu_ilu *h);
 BDILU_API int bdilu_host_dot_vec(const double *host_data, int nblocks, int blockw, int ndiag, int nsat, int ld,
                        const double *host_vec, double *host_out, int nrhs);
 
+/* BlockDiagMatrix::scale_diag_add / set_to_eye_plus_scaled_mtx on HOST memory (block_diag_ilu.hpp:276-290),
+ * one system; host_dst may equal host_src. */
+BDILU_API int bdilu_host_scale_diag_add(double *host_dst, const double *host_src, int nblocks, int blockw,
+                              int ndiag, int nsat, int ld, double scale, double diag_add);
+
 /* One-shot ILU(A) + solve(b, x) on HOST memory for a batch: H2D of data and b, fused factor +
  * solve, D2H of x (and flags / info).  host_data is NOT modified (ILU copies its source). */
 BDILU_API int bdilu_host_factor_solve(const double *host_data, int64_t sys_stride, int nsys,
