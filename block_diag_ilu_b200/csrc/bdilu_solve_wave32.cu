@@ -12,23 +12,32 @@
 //     to publish finished values and to poll the predecessors' ring slots.
 //   * step k: lane k publishes its finished value (one predicated store) and broadcasts it by shuffle; every
 //     lane then does one unpredicated DFMA with the block entry in column k.  Lanes that are already finished
-//     pick up garbage from that DFMA -- they are dead: a lane's result is read back from the ring slot it
-//     published to.
-//   * coupling: every PB steps all lanes load their predecessors' entries (branch-free); only the PB lanes
-//     whose turn comes LA steps later use them, after a warp vote that they are really there ("not yet
-//     written" is an in-band signalling-NaN pattern).  The coupling is applied at that fixed step, so the
-//     result is bit-reproducible.
+//     pick up garbage from that DFMA -- they are dead: a lane's result was captured when it was published.
+//   * coupling: two accumulators (even / odd sweep positions) keep the coupling terms off the dependency chain;
+//     "not yet written" is an in-band signalling-NaN pattern in the shared-memory ring, polled one step ahead by
+//     a warp-uniform vote.  The coupling is applied at a fixed step, so the result is bit-reproducible.
 //   * U rows are pre-scaled by 1/U[r][r], so the backward chain has no division on it.
 // Blocks "before the first" are virtual ring slots holding zeros, so every block sees exactly ND predecessors.
-#include <cstdlib>
-
 #include "bdilu_wave_common.cuh"
 
 namespace bdilu {
 
 namespace wave {
 
-constexpr int RS = 2 * NW;  // ring slots (power of two)
+// Phase profile (debug builds only, -DBDILU_W32_PROF): cycles summed over consumer warps / the producer warp.
+//   [0] wait for the stage  [1] stage -> registers  [2] first coupling poll  [3] the 32-step chain  [4] store
+//   [5] producer: wait for an empty stage  [6] producer: issue  [7] blocks counted
+#ifdef BDILU_W32_PROF
+__device__ unsigned long long g_w32prof[8];
+#define W32_T(var) const long long var = clock64()
+#define W32_ADD(slot, a, b) if (r == 0) atomicAdd(&g_w32prof[slot], (unsigned long long)((b) - (a)))
+#else
+#define W32_T(var)
+#define W32_ADD(slot, a, b)
+#endif
+
+constexpr int RS = 32;  // ring slots (power of two, >= NW + MAXD + 1)
+static_assert(NW + MAXD + 1 <= RS, "ring too small for the reset protocol");
 
 __device__ __forceinline__ void ring_reset(const Smem &S, int tid, int nthreads, int nd)
 {
@@ -36,7 +45,6 @@ __device__ __forceinline__ void ring_reset(const Smem &S, int tid, int nthreads,
         const int slot = t >> 5;
         S.ring[t] = (slot >= RS - nd) ? 0.0 : __longlong_as_double((long long)SENT);
     }
-    if (tid < NW) S.done[tid] = 0;
 }
 
 // ---- producer warp: lane = piece ---------------------------------------------------------------------------
@@ -85,12 +93,20 @@ __device__ void produce32(const Args &A, const Smem &S, int s, unsigned ph, bool
     const unsigned tx_fixed = A.SL.blk_bytes + A.SL.idx_bytes + (FWD ? A.SL.idx_bytes + A.SL.vec_bytes : 0);
     bool reuse = !first_pass;  // stages were used before: wait for the consumers' release
     for (int i = 0; i < N; ++i) {
+#ifdef BDILU_W32_PROF
+        const int r = lane;
+#endif
+        W32_T(p0);
         if (reuse) mbar_wait(&S.empty[s], ph ^ 1u);
+        W32_T(p1);
         unsigned char *stg = S.stages + (size_t)s * A.SL.bytes;
         const int nd = min(ND, i);
         if (lane == 0) mbar_expect_tx(&S.full[s], tx_fixed + nd * A.SL.diag_bytes);
         if (bytes != 0 && dmine < nd) bulk_g2s(stg + dst, src, bytes, &S.full[s]);
         src += inc;
+        W32_T(p2);
+        W32_ADD(5, p0, p1);
+        W32_ADD(6, p1, p2);
         if (++s == A.NS) {
             s = 0;
             ph ^= 1u;
@@ -100,7 +116,21 @@ __device__ void produce32(const Args &A, const Smem &S, int s, unsigned ph, bool
 }
 
 // ---- consumers -----------------------------------------------------------------------------------------------
-template <bool FWD, int ND, int LA, int PB>
+// Ring protocol (RS = 32 slots of 32 doubles, slot of block order i = i & 31):
+//   * block i publishes row values into slot i, polls slots i-1 .. i-ND ("not yet written" = SENT);
+//   * after its LAST coupling read, and BEFORE it publishes its last rows, block i resets slot i-ND to SENT.  When
+//     block i has read everything it needs, blocks i-1 .. i-ND+1 have published everything, hence finished reading
+//     slot i-ND too (every row is read before the row that needs it is published), so block i is the last reader.
+//     The next writer of that slot, block i-ND+32, is started by a warp that first finished block i-ND+32-NW >= i+1
+//     (NW + ND + 1 <= 32), which cannot complete before block i published its last rows -> the reset is ordered
+//     before the reuse, with no counters and no extra waiting.
+//
+// Dependency chain of one block = 32 x (shuffle broadcast + one DFMA).  Nothing else touches the register the chain
+// runs through: positions of even parity accumulate in accA, odd ones in accB; step kk broadcasts from the register of
+// parity kk, updates the register of parity kk+1 first (the next step reads it) and only then the other one, into which
+// the coupling terms of position kk+2 are merged while that register has a whole step of slack.  The predecessor
+// values for that merge were loaded one step earlier, so the poll costs no latency unless the predecessor is late.
+template <bool FWD, int ND>
 __device__ void consume32(const Args &A, const Smem &S, int s0, unsigned ph0, int j, int r, int &nan_first,
                           int &zero_last)
 {
@@ -116,24 +146,16 @@ __device__ void consume32(const Args &A, const Smem &S, int s0, unsigned ph0, in
         s -= A.NS;
         ph ^= 1u;
     }
+    const int q = FWD ? r : W - 1 - r;  // position of my row in sweep order
 
     for (int i = j; i < N; i += NW) {
         const int b = FWD ? i : N - 1 - i;
-        // Recycle the ring slot my next block (order i+NW) will publish into: it holds the values of order
-        // i-NW (or a virtual block); their readers are orders i-NW+1 .. i-NW+ND, which must have completed.
-#pragma unroll
-        for (int d = 0; d < ND; ++d) {
-            const int oi = i - NW + 1 + d;
-            if (oi >= 0 && oi < N)
-                while (ld_volatile_s(&S.done[oi & (NW - 1)]) < oi + 1) {
-                }
-        }
-        st_volatile_s(&S.ring[((i + NW) & (RS - 1)) * 32 + r], __longlong_as_double((long long)SENT));
-
         const double y_cur = ynext;
         if (!FWD && i + NW < N) ynext = A.x[(int64_t)(N - 1 - (i + NW)) * W + r];
 
+        W32_T(t0);
         mbar_wait(&S.full[s], ph);
+        W32_T(t1);
         const unsigned char *st = S.stages + (size_t)s * A.SL.bytes;
         const double *Ls = reinterpret_cast<const double *>(st);
         double l[W];
@@ -171,47 +193,73 @@ __device__ void consume32(const Args &A, const Smem &S, int s0, unsigned ph0, in
         }
 
         double *myslot = S.ring + (i & (RS - 1)) * 32;
+        double *resetslot = S.ring + ((i - ND) & (RS - 1)) * 32 + r;
         const double *pd[ND];
 #pragma unroll
         for (int d = 0; d < ND; ++d) pd[d] = S.ring + ((i - 1 - d) & (RS - 1)) * 32 + ci;
 
-        // Coupling of the rows [lo, lo+cnt) in sweep order (row r sits at sweep position q = r or W-1-r).
-        const int q = FWD ? r : W - 1 - r;
-        auto couple = [&](int lo, int cnt) {
-            // warp-uniform retry loop: no lane ever spins on its own, so the warp never splits
-            const bool mine = (unsigned)(q - lo) < (unsigned)cnt;
-            double v[ND];
+        double v[ND];
+        auto load_pred = [&]() {
+#pragma unroll
+            for (int d = 0; d < ND; ++d) v[d] = ld_volatile_s(pd[d]);
+        };
+        // Warp-uniform wait until the lanes selected by `mine` hold real predecessor values in v[] (no lane ever
+        // spins on its own, so the warp never splits); the first test uses the values loaded a step earlier.
+        auto await_pred = [&](bool mine) {
             for (;;) {
                 bool bad = false;
 #pragma unroll
-                for (int d = 0; d < ND; ++d) {
-                    v[d] = ld_volatile_s(pd[d]);
-                    bad |= is_sent(v[d]);
-                }
+                for (int d = 0; d < ND; ++d) bad |= is_sent(v[d]);
                 if (!__any_sync(FULL, mine && bad)) break;
-            }
-#pragma unroll
-            for (int d = ND - 1; d >= 0; --d) {
-                const double t = fma(-cv[d], v[d], acc);
-                acc = mine ? t : acc;
+                load_pred();
             }
         };
-        couple(0, LA);
+        auto coupled = [&](double a) {
+#pragma unroll
+            for (int d = ND - 1; d >= 0; --d) a = fma(-cv[d], v[d], a);
+            return a;
+        };
+
+        // positions 0 and 1 take their coupling terms before the chain starts
+        W32_T(t2);
+        load_pred();
+        await_pred(q < 2);
+        W32_T(t3);
+        if (q < 2) acc = coupled(acc);
+        double accA = acc, accB = acc, mine_final = acc;
+        load_pred();
 #pragma unroll
         for (int kk = 0; kk < W; ++kk) {
             const int k = FWD ? kk : W - 1 - kk;
-            if (r == k) st_volatile_s(&myslot[k], acc);
-            const double vk = group_bcast<32>(acc, k);
-            if (kk % PB == 0 && kk + LA < W) couple(kk + LA, PB);
-            if (kk + 1 < W) acc = fma(-l[k], vk, acc);
+            double &cur = (kk & 1) ? accB : accA;   // holds the finished value of position kk (in lane k)
+            double &nxt = (kk & 1) ? accA : accB;   // read by the next step: update it first
+            if (r == k) {
+                st_volatile_s(&myslot[k], cur);
+                mine_final = cur;
+            }
+            const double vk = group_bcast<32>(cur, k);
+            if (kk + 1 < W) nxt = fma(-l[k], vk, nxt);
+            if (kk + 2 < W) {
+                cur = fma(-l[k], vk, cur);
+                await_pred(q == kk + 2);
+                if (q == kk + 2) cur = coupled(cur);
+                if (kk + 3 < W) load_pred();
+                else st_volatile_s(resetslot, __longlong_as_double((long long)SENT));  // all my reads are done
+            }
         }
-        __syncwarp();
-        A.x[(int64_t)b * W + r] = ld_volatile_s(&myslot[r]);
-        if (r == 0) st_volatile_s(&S.done[j], i + 1);
+        W32_T(t4);
+        A.x[(int64_t)b * W + r] = mine_final;
+        W32_T(t5);
+        W32_ADD(0, t0, t1);
+        W32_ADD(1, t1, t2);
+        W32_ADD(2, t2, t3);
+        W32_ADD(3, t3, t4);
+        W32_ADD(4, t4, t5);
+        W32_ADD(7, 0, 1);
     }
 }
 
-template <int ND, int LA, int PB>
+template <int ND>
 __global__ void __launch_bounds__((NW + 1) * 32, 1)
 solve_wave32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                     const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
@@ -266,7 +314,7 @@ solve_wave32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     if (warp == NW) {
         produce32<true, ND>(A, S, 0, 0u, true, lane);
     } else {
-        consume32<true, ND, LA, PB>(A, S, 0, 0u, warp, lane, nan_first, zero_last);
+        consume32<true, ND>(A, S, 0, 0u, warp, lane, nan_first, zero_last);
     }
     __syncthreads();  // y (in the x buffer) is complete and visible to the whole CTA
     ring_reset(S, tid, blockDim.x, ND);
@@ -274,7 +322,7 @@ solve_wave32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     if (warp == NW) {
         produce32<false, ND>(A, S, s_bwd, ph_bwd, N < NS, lane);
     } else {
-        consume32<false, ND, LA, PB>(A, S, s_bwd, ph_bwd, warp, lane, nan_first, zero_last);
+        consume32<false, ND>(A, S, s_bwd, ph_bwd, warp, lane, nan_first, zero_last);
     }
     if (warp < NW) {
 #pragma unroll
@@ -294,20 +342,32 @@ solve_wave32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     }
 }
 
-template <int ND, int LA, int PB>
+template <int ND>
 static cudaError_t launch_cfg(unsigned nvec, size_t smem, cudaStream_t st, const double *data, int64_t sys_stride,
                               const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
                               const VecLayout &V, int *flags, int NS)
 {
-    cudaError_t e = cudaFuncSetAttribute(solve_wave32_kernel<ND, LA, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(solve_wave32_kernel<ND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          227 * 1024);
     if (e != cudaSuccess) return e;
-    solve_wave32_kernel<ND, LA, PB><<<nvec, (NW + 1) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V,
+    solve_wave32_kernel<ND><<<nvec, (NW + 1) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V,
                                                                        flags, NS);
     return cudaGetLastError();
 }
 
 }  // namespace wave
+
+#ifdef BDILU_W32_PROF
+extern "C" __attribute__((visibility("default"))) int bdilu_debug_w32prof(unsigned long long *out8, int reset)
+{
+    if (out8) cudaMemcpyFromSymbol(out8, wave::g_w32prof, sizeof(unsigned long long) * 8);
+    if (reset) {
+        unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        cudaMemcpyToSymbol(wave::g_w32prof, z, sizeof z);
+    }
+    return 0;
+}
+#endif
 
 // blockw == 32, 1 <= ndiag <= 4; the caller has checked alignment and sizes (try_launch_solve_wave).
 cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double *data, int64_t sys_stride, const Dims &D,
@@ -315,21 +375,12 @@ cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double
                                 const VecLayout &V, int *flags, cudaStream_t st)
 {
     using namespace wave;
-#define BDILU_W32(ND_, LA_, PB_) \
-    return launch_cfg<ND_, LA_, PB_>(nvec, smem, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, NS);
+#define BDILU_W32(ND_) return launch_cfg<ND_>(nvec, smem, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, NS);
     switch (D.ndiag) {
-    case 1: BDILU_W32(1, 2, 1)
-    case 2: {
-        const char *e = getenv("BDILU_W32CFG");
-        const int cfg = e ? atoi(e) : 0;
-        if (cfg == 1) BDILU_W32(2, 1, 2)
-        if (cfg == 2) BDILU_W32(2, 2, 2)
-        if (cfg == 3) BDILU_W32(2, 2, 4)
-        if (cfg == 4) BDILU_W32(2, 3, 1)
-        BDILU_W32(2, 2, 1)
-    }
-    case 3: BDILU_W32(3, 2, 1)
-    default: BDILU_W32(4, 2, 1)
+    case 1: BDILU_W32(1)
+    case 2: BDILU_W32(2)
+    case 3: BDILU_W32(3)
+    default: BDILU_W32(4)
     }
 #undef BDILU_W32
 }
