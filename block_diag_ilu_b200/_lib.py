@@ -51,7 +51,7 @@ def lib():
     """Load (building first if needed) the shared library.  Raises if it cannot be had."""
     global _lib
     if _lib is None:
-        path = _build.build()
+        path = os.environ.get("BDILU_LIB_PATH") or _build.build()  # override: instrumented debug builds
         L = C.CDLL(path)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(L, name)  # AttributeError here == ABI drift: fail loudly

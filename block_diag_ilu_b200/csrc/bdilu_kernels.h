@@ -23,7 +23,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
-extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel
+extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel
 bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                            cudaStream_t st, cudaError_t *err);
@@ -31,6 +31,10 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
 cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double *data, int64_t sys_stride, const Dims &D,
                                 const int *rowbycol, const int *colbyrow, const double *b, double *x,
                                 const VecLayout &V, int *flags, cudaStream_t st);
+
+bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
+                             const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
+                             cudaStream_t st, cudaError_t *err);
 
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st);

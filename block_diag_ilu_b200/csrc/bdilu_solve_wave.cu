@@ -255,6 +255,11 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
         if (*err != cudaSuccess) return true;
         attr_set = true;
     }
+    if (w == 32 && g_solve_path == 0 &&
+        try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err)) {
+        count_launch(1);
+        return true;
+    }
     if (w == 32 && g_solve_path != 2) {
         *err = launch_solve_wave32((unsigned)nvec, smem, NS, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st);
         count_launch(1);

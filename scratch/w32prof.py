@@ -10,11 +10,11 @@ L = _lib.lib()
 ilu = dev.BatchedILU(data.clone(), N, w, d)
 x = ilu.solve(b); torch.cuda.synchronize()
 out = (C.c_ulonglong * 8)()
-L.bdilu_debug_w32prof(out, 1)
+L.bdilu_debug_q32prof(out, 1)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); x = ilu.solve(b); e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
-L.bdilu_debug_w32prof(out, 0)
+L.bdilu_debug_q32prof(out, 0)
 v = list(out)
 nb = v[7]
 names = ["wait_stage", "to_regs", "first_poll", "chain", "store", "prod_wait_empty", "prod_issue"]

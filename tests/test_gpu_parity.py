@@ -91,12 +91,12 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-@pytest.fixture(params=["auto", "chain", "wave_generic"])
+@pytest.fixture(params=["auto", "chain", "wave_generic", "wave32_onerow"])
 def solve_path(request):
-    """Run the case on the automatically chosen solve kernel (wave32 / generic wavefront where they apply),
-    on the general chain kernel, and on the generic wavefront kernel."""
+    """Run the case on the automatically chosen solve kernel (quad32 / generic wavefront where they apply),
+    on the general chain kernel, on the generic wavefront kernel, and on the one-row-per-step wave32 kernel."""
     from block_diag_ilu_b200 import _lib
-    old = _lib.lib().bdilu_debug_force_chain_solve({"auto": 0, "chain": 1, "wave_generic": 2}[request.param])
+    old = _lib.lib().bdilu_debug_force_chain_solve({"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3}[request.param])
     yield request.param
     _lib.lib().bdilu_debug_force_chain_solve(old)
 
@@ -106,7 +106,8 @@ def test_config3_shape_subset(oracle, solve_path):
     run_case(oracle, 1, 2048, 32, 2, "P", seed0=77, yardstick=True)
 
 
-@pytest.mark.parametrize("N,w,d,ld", [(64, 32, 1, 32), (200, 32, 2, 32), (333, 32, 3, 34), (100, 16, 1, 16),
+@pytest.mark.parametrize("N,w,d,ld", [(64, 32, 1, 32), (200, 32, 2, 32), (333, 32, 3, 34), (67, 32, 4, 32), (130, 32, 2, 40),
+                                      (65, 32, 1, 32), (100, 16, 1, 16),
                                       (129, 8, 2, 8), (77, 24, 4, 24), (640, 4, 1, 4), (90, 20, 2, 22)])
 @pytest.mark.parametrize("fam", ["D", "P"])
 def test_wavefront_shapes(oracle, solve_path, N, w, d, ld, fam):
