@@ -96,6 +96,8 @@ __device__ __forceinline__ unsigned group_min_u(unsigned v)
 struct RowState {
     int pos, ipiv, info;
     double diag;
+    double rinv;  // correctly rounded 1/diag when `fast` (lean path), unused otherwise
+    bool fast;
 };
 
 // Stores what one lane owns after the elimination: its row of L\U at row `pos`, the permutation
@@ -106,6 +108,15 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
                                             int *__restrict__ ipiv, int *__restrict__ rowbycol,
                                             int *__restrict__ colbyrow, int *__restrict__ info)
 {
+    // sub(di,bi,c) /= U[c][c]  (block_diag_ilu.hpp:471-475): the loads go out first so that their latency hides
+    // behind the column stores; the quotient is s*rinv corrected by one FMA pair (Markstein: correctly rounded when
+    // rinv is the correctly rounded reciprocal), a true division only for a zero / out-of-range diagonal.
+    constexpr int PF = 2;  // sub rows prefetched into registers
+    const int nsub = min(D.ndiag, D.nblocks - 1 - bi);
+    double sv[PF];
+#pragma unroll
+    for (int di = 0; di < PF; ++di)
+        sv[di] = (di < nsub) ? sysdata[D.off_sub + D.diag_chunk(di, bi) + r] : 0.0;
 #pragma unroll
     for (int c = 0; c < WP; ++c)
         if (c < w) blk[(int64_t)c * ld + S.pos] = a[c];
@@ -113,16 +124,24 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
     ipiv[ib + r] = S.ipiv;
     rowbycol[ib + S.pos] = r;
     colbyrow[ib + r] = S.pos;
-    // sub(di,bi,c) /= U[c][c]  (block_diag_ilu.hpp:471-475)
-    for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
-        double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
-        *s = *s / S.diag;
+    const bool fastq = S.fast && S.diag != 0.0;
+    auto quot = [&](double sval) {
+        if (!fastq) return sval / S.diag;
+        double qv = sval * S.rinv;
+        return fma(fma(-qv, S.diag, sval), S.rinv, qv);
+    };
+#pragma unroll
+    for (int di = 0; di < PF; ++di)
+        if (di < nsub) sysdata[D.off_sub + D.diag_chunk(di, bi) + r] = quot(sv[di]);
+    for (int di = PF; di < nsub; ++di) {
+        double *sp = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
+        *sp = quot(*sp);
     }
     // bot(sati,bi,c) /= U[c][c]  (:476-479)
     if (bi < D.nsat)
         for (int sati = bi; sati < D.nsat; ++sati) {
-            double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
-            *s = *s / S.diag;
+            double *sp = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
+            *sp = *sp / S.diag;
         }
     if (S.info != 0 && r == 0) {
         // keep the failing block with the lowest index (serial loop order, :469-470)
@@ -151,7 +170,7 @@ __device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dim
     for (int c = 0; c < WP; ++c)
         a[c] = (rowok && c < w) ? blk[(int64_t)c * ld + r] : ((c == r) ? 1.0 : 0.0);
     RowState S;
-    S.pos = r; S.ipiv = r + 1; S.info = 0; S.diag = 1.0;
+    S.pos = r; S.ipiv = r + 1; S.info = 0; S.diag = 1.0; S.rinv = 1.0; S.fast = false;
     bool active = rowok;
     for (int k = 0; k < w; ++k) {
         const double v = active ? fabs(a[k]) : -1.0;
@@ -214,7 +233,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
 
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const int grp = lane / G, r = lane % G;
-    const int w = EXACT ? WP : D.w, ld = D.ld;
+    const int w = EXACT ? WP : D.w, ld = EXACT ? WP : D.ld;  // EXACT: w == ld == WP, all offsets are immediates
     const int64_t total = (int64_t)nsys * D.nblocks;
     int64_t gb = ((int64_t)blockIdx.x * FACTOR_WARPS + wic) * BPW + grp;
     const bool live = gb < total;  // dead groups run on the last block but store nothing
@@ -236,6 +255,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     bool active = true;   // not yet chosen as a pivot row (padded rows take part: see above)
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
     double my_diag = 1.0; // lane k keeps U[k][k]
+    double my_rinv = 1.0; // ... and its correctly rounded reciprocal
     int my_info = 0;
     bool weird = false;
 
@@ -276,7 +296,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
         const int ehi = (__double2hiint(piv) >> 20) & 0x7ff;
         const bool nz = (piv != 0.0);
         weird |= nz && (ehi < 0x020 || ehi > 0x7dd);
-        if (r == k) my_diag = piv;
+        if (r == k) { my_diag = piv; my_rinv = rinv; }
         if (!nz && my_info == 0) my_info = k + 1;  // dgetf2: record, leave the column unscaled
 
         // ---- multiplier by (exactly rounded) division, rank-1 update of the trailing columns ----
@@ -296,7 +316,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     }
     if (live && rowok) {
         RowState S;
-        S.pos = pos; S.ipiv = my_ipiv; S.info = my_info; S.diag = my_diag;
+        S.pos = pos; S.ipiv = my_ipiv; S.info = my_info; S.diag = my_diag; S.rinv = my_rinv; S.fast = true;
         store_block<WP>(a, S, sysdata, blk, D, w, ld, sys, bi, r, ipiv, rowbycol, colbyrow, info);
     }
 }
@@ -413,7 +433,7 @@ cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims
     {                                                                                              \
         const int64_t per_cta = (int64_t)FACTOR_WARPS * (32 / WP);                                 \
         const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);                         \
-        if (D.w == WP)                                                                             \
+        if (D.w == WP && D.ld == WP)                                                               \
             factor_kernel<WP, true><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, \
                                                                         rowbycol, colbyrow, info);  \
         else                                                                                       \

@@ -141,8 +141,13 @@ __device__ void produce(const Ctx &C, int p, int lane)
         unsigned bytes = 0, dst = 0;
         if (lane == 0) {
             src = reinterpret_cast<const char *>(C.sd + C.D.block(b_lo));
-            bytes = nb * GL.blk_bytes;
+            bytes = ((C.dbg & 4) ? 1 : nb) * GL.blk_bytes;
             dst = mo * GL.blk_bytes;
+        } else if ((C.dbg & 4) && lane >= 8 && lane < 8 + nb - 1) {
+            const int k = lane - 7;  // blocks 1..nb-1 of the group, one copy each
+            src = reinterpret_cast<const char *>(C.sd + C.D.block(b_lo + k));
+            bytes = GL.blk_bytes;
+            dst = (mo + k) * GL.blk_bytes;
         } else if (lane == 1) {
             src = reinterpret_cast<const char *>(C.cbr + (int64_t)b_lo * W);
             bytes = nb * W * 4;
@@ -188,13 +193,17 @@ __device__ void produce(const Ctx &C, int p, int lane)
 //     The next writer of that slot, block i-ND+32, is started by a warp that first finished block i-ND+32-QW >= i+1
 //     (QW + ND + 1 <= 32), which cannot complete before block i published its last quad -> the reset is ordered
 //     before the reuse, with no counters and no extra waiting.
-template <bool FWD, int ND>
+// MODE 0: quads by shuffle (every lane solves the 4x4 triangle);  MODE 4 / 2 / 1: lean chain, one row per step
+// through shared memory, coupling merged every 4 / 2 / 1 rows.
+template <bool FWD, int ND, int MODE>
 __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_last)
 {
     const int N = C.D.nblocks, ld = C.D.ld;
     const GroupLayout &GL = C.GL;
     const int q = FWD ? r : W - 1 - r;  // position of my row in sweep order
-    const int myquad = q >> 2;
+    constexpr int PG = (MODE == 0) ? 4 : MODE;  // rows per coupling group
+    constexpr int NGRP = W / PG;
+    const int myquad = q / PG;              // coupling group of my row
     // phase numbering of the "started" barriers: forward blocks count from 0, backward blocks from 32*ceil(N/32)
     const int ibase = FWD ? 0 : ((N + RS - 1) & ~(RS - 1));
     double ynext = 0.0;
@@ -273,19 +282,21 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
         // its own, so the warp never splits); the first test uses values loaded before the previous quad's shuffles.
         auto merge_quad = [&](int qd) {
             const bool mine = (myquad == qd);
+            double t;
             Q32_GUARD_DECL;
             for (;;) {
                 Q32_GUARD(FWD ? "merge fwd" : "merge bwd", i, qd, ci)
+                // speculative: the DFMAs run while the vote below decides whether v[] was real
+                t = acc;
+#pragma unroll
+                for (int d = ND - 1; d >= 0; --d) t = fma(-cv[d], v[d], t);
                 bool bad = false;
 #pragma unroll
                 for (int d = 0; d < ND; ++d) bad |= is_sent(v[d]);
                 if (!__any_sync(FULL, mine && bad)) break;
                 load_pred(qd);
             }
-            double cs = cv[0] * v[0];
-#pragma unroll
-            for (int d = 1; d < ND; ++d) cs = fma(cv[d], v[d], cs);
-            if (mine) acc -= cs;
+            if (mine) acc = t;
         };
         // sweep positions 4*jq .. 4*jq+3 live in lanes LN(jq, 0..3); CF(jq, n) is my coefficient for position 4*jq+n
 #define LN(jq, n) (FWD ? 4 * (jq) + (n) : W - 1 - (4 * (jq) + (n)))
@@ -300,43 +311,71 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
             t[5] = group_bcast<32>(CF(jq, 2), LN(jq, 3));
         };
 
-        // Sleep (mbarrier, no polling traffic) until my predecessor has published its first quad; from then on it
-        // stays about one quad ahead of me and the in-band polls below almost always succeed at once.
+        // Sleep (mbarrier, no polling traffic) until my predecessor has published its first group; from then on it
+        // stays about one group ahead of me and the in-band polls below almost always succeed at once.
         mbar_wait_guard(&C.started[(i - 1) & (RS - 1)], (unsigned)((ibase + i - 1) >> 5) & 1u,
                         FWD ? "started fwd" : "started bwd", i, 0, 0);
         load_pred(0);
-        double tri[6];
-        triangle(0, tri);
-        merge_quad(0);
-        Q32_T(t3);
+        if constexpr (MODE == 0) {
+            double tri[6];
+            triangle(0, tri);
+            merge_quad(0);
+            Q32_T(t3);
 #pragma unroll
-        for (int j4 = 0; j4 < W / 4; ++j4) {
-            if (j4 + 1 < W / 4) load_pred(j4 + 1);  // for the merge at the end of this step
-            const double a0 = group_bcast<32>(acc, LN(j4, 0));
-            const double a1 = group_bcast<32>(acc, LN(j4, 1));
-            const double a2 = group_bcast<32>(acc, LN(j4, 2));
-            const double a3 = group_bcast<32>(acc, LN(j4, 3));
-            double trin[6];
-            if (j4 + 1 < W / 4) triangle(j4 + 1, trin);  // next step's triangle: fills the shuffle latency
-            const double y0 = a0;
-            const double y1 = fma(-tri[0], y0, a1);
-            const double y2 = fma(-tri[2], y1, fma(-tri[1], y0, a2));
-            const double y3 = fma(-tri[5], y2, fma(-tri[4], y1, fma(-tri[3], y0, a3)));
-            acc = fma(-CF(j4, 0), y0, acc);
-            acc = fma(-CF(j4, 1), y1, acc);
-            acc = fma(-CF(j4, 2), y2, acc);
-            acc = fma(-CF(j4, 3), y3, acc);
-            if (myquad == j4) st_volatile_s(myslot, acc);
-            if (j4 == 0) {
-                __syncwarp();
-                if (r == 0) mbar_arrive(&C.started[i & (RS - 1)]);
+            for (int j4 = 0; j4 < W / 4; ++j4) {
+                if (j4 + 1 < W / 4) load_pred(j4 + 1);  // for the merge at the end of this step
+                const double a0 = group_bcast<32>(acc, LN(j4, 0));
+                const double a1 = group_bcast<32>(acc, LN(j4, 1));
+                const double a2 = group_bcast<32>(acc, LN(j4, 2));
+                const double a3 = group_bcast<32>(acc, LN(j4, 3));
+                double trin[6];
+                if (j4 + 1 < W / 4) triangle(j4 + 1, trin);  // next step's triangle: fills the shuffle latency
+                const double y0 = a0;
+                const double y1 = fma(-tri[0], y0, a1);
+                const double y2 = fma(-tri[2], y1, fma(-tri[1], y0, a2));
+                const double y3 = fma(-tri[5], y2, fma(-tri[4], y1, fma(-tri[3], y0, a3)));
+                acc = fma(-CF(j4, 0), y0, acc);
+                acc = fma(-CF(j4, 1), y1, acc);
+                acc = fma(-CF(j4, 2), y2, acc);
+                acc = fma(-CF(j4, 3), y3, acc);
+                if (myquad == j4) st_volatile_s(myslot, acc);
+                if (j4 == 0) {
+                    __syncwarp();
+                    if (r == 0) mbar_arrive(&C.started[i & (RS - 1)]);
+                }
+                if (j4 + 1 < W / 4) {
+                    merge_quad(j4 + 1);
+                    if (j4 + 2 == W / 4)  // all my coupling reads are done: recycle the slot of block i-ND
+                        st_volatile_s(resetslot, __longlong_as_double((long long)SENT));
+#pragma unroll
+                    for (int e = 0; e < 6; ++e) tri[e] = trin[e];
+                }
             }
-            if (j4 + 1 < W / 4) {
-                merge_quad(j4 + 1);
-                if (j4 + 2 == W / 4)  // all my coupling reads are done: recycle the slot of block i-ND
-                    st_volatile_s(resetslot, __longlong_as_double((long long)SENT));
+        } else {
+            // Lean chain: the lane whose row is finished stores it into the ring (that store IS the publication) and
+            // everybody reads it back with one broadcast load: three instructions per row, no shuffles, no selects.
+            merge_quad(0);
+            Q32_T(t3);
+            const double *slotbase = C.ring + (i & (RS - 1)) * 32;
 #pragma unroll
-                for (int e = 0; e < 6; ++e) tri[e] = trin[e];
+            for (int kk = 0; kk < W; ++kk) {
+                const int k = FWD ? kk : W - 1 - kk;
+                const int g = kk / PG;
+                if (kk % PG == 0 && g + 1 < NGRP) load_pred(g + 1);  // for the merge at the end of this group
+                if (r == k) st_volatile_s(myslot, acc);
+                if (kk + 1 < W) {
+                    const double vk = ld_volatile_s(slotbase + k);
+                    acc = fma(-l[k], vk, acc);
+                }
+                if (kk == PG - 1) {
+                    __syncwarp();
+                    if (r == 0) mbar_arrive(&C.started[i & (RS - 1)]);
+                }
+                if (kk % PG == PG - 1 && g + 1 < NGRP) {
+                    merge_quad(g + 1);
+                    if (g + 2 == NGRP)  // all my coupling reads are done: recycle the slot of block i-ND
+                        st_volatile_s(resetslot, __longlong_as_double((long long)SENT));
+                }
             }
         }
 #undef LN
@@ -353,7 +392,7 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
     }
 }
 
-template <int ND>
+template <int ND, int MODE>
 __global__ void __launch_bounds__((QW + NP) * 32, 1)
 solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                     const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
@@ -403,7 +442,7 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
 
     int nan_first = 0x7fffffff, zero_last = -1;
     if (warp >= QW) produce<true, ND>(C, warp - QW, lane);
-    else consume<true, ND>(C, warp, lane, nan_first, zero_last);
+    else consume<true, ND, MODE>(C, warp, lane, nan_first, zero_last);
     __syncthreads();  // y (in the x buffer) is complete and visible to the whole CTA
     ring_reset(C, tid, blockDim.x, ND);
     // "started" barriers keep counting phases across the sweeps: slots that saw one block fewer in the forward sweep
@@ -412,7 +451,7 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     if (tid < RS && (N & (RS - 1)) != 0 && tid >= (N & (RS - 1))) mbar_arrive(&C.started[tid]);
     __syncthreads();
     if (warp >= QW) produce<false, ND>(C, warp - QW, lane);
-    else consume<false, ND>(C, warp, lane, nan_first, zero_last);
+    else consume<false, ND, MODE>(C, warp, lane, nan_first, zero_last);
     if (warp < QW) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -431,16 +470,39 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     }
 }
 
+// BDILU_QUAD_DBG (read once): timing experiments only (every variant gives correct results).
+//   2 = one producer warp, 4 = one bulk copy per block instead of per group,
+//   32 / 64 / 128 = chain variant: shuffle quads (32), lean chain merging the coupling every 4 rows (64) or every
+//   row (128); default: lean chain, every 2 rows (the fastest on B200, see profiles/)
+static int debug_switches()
+{
+    static const int v = getenv("BDILU_QUAD_DBG") ? atoi(getenv("BDILU_QUAD_DBG")) : 0;
+    return v;
+}
+
+template <int ND, int MODE>
+static cudaError_t launch_mode(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
+                               const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
+                               const VecLayout &V, int *flags)
+{
+    cudaError_t e = cudaFuncSetAttribute(solve_quad32_kernel<ND, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         227 * 1024);
+    if (e != cudaSuccess) return e;
+    solve_quad32_kernel<ND, MODE><<<nvec, (QW + NP) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V,
+                                                                      flags, NS, debug_switches());
+    return cudaGetLastError();
+}
+
 template <int ND>
 static cudaError_t launch_nd(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
                              const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
                              const VecLayout &V, int *flags)
 {
-    cudaError_t e = cudaFuncSetAttribute(solve_quad32_kernel<ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return e;
-    solve_quad32_kernel<ND><<<nvec, (QW + NP) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, NS,
-                                                                getenv("BDILU_QUAD_DBG") ? atoi(getenv("BDILU_QUAD_DBG")) : 0);
-    return cudaGetLastError();
+    const int dbg = debug_switches();
+    if (dbg & 32) return launch_mode<ND, 0>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
+    if (dbg & 128) return launch_mode<ND, 1>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
+    if (dbg & 64) return launch_mode<ND, 4>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
+    return launch_mode<ND, 2>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
 }
 
 }  // namespace quad
