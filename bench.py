@@ -60,6 +60,19 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(kernel, nsys):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
+    capture of this workload (profiles/traffic.json, written by tools/ncu_traffic.py); None when there is none or
+    when it was taken on another batch size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        e = t["kernels"][kernel]
+        return float(e["dram_bytes"]) if int(e["nsys"]) == int(nsys) else None
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons through NVML while the timed regions run."""
 
@@ -269,8 +282,10 @@ def run_ours(args, rank, world, local_rank):
     dom_ms = max(kf, ks)
     achieved = nsys * AB[dom] / (dom_ms * 1e-3) / 1e9
     fused_gbs = nsys * AB["fused"] / (ms_per_step * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "factor_kernel<32>" if dom == "factor" else "solve kernel",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    kname = "factor_kernel<32,1>" if dom == "factor" else "solve_quad32_kernel<2,2>"
+    roofline = {"bound": "hbm", "kernel": kname,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(kname, nsys),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": nsys * AB[dom],
                 "kernel_ms": {"factor": kf, "solve": ks},
                 "fused_step": {"achieved": fused_gbs, "frac": fused_gbs / peak,

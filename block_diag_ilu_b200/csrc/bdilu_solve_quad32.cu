@@ -195,10 +195,10 @@ __device__ void produce(const Ctx &C, int p, int lane)
 //     before the reuse, with no counters and no extra waiting.
 // MODE 0: quads by shuffle (every lane solves the 4x4 triangle);  MODE 4 / 2 / 1: lean chain, one row per step
 // through shared memory, coupling merged every 4 / 2 / 1 rows.
-template <bool FWD, int ND, int MODE>
+template <bool FWD, int ND, int MODE, bool LD32>
 __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_last)
 {
-    const int N = C.D.nblocks, ld = C.D.ld;
+    const int N = C.D.nblocks, ld = LD32 ? W : C.D.ld;  // LD32: tight blocks, every stage offset is an immediate
     const GroupLayout &GL = C.GL;
     const int q = FWD ? r : W - 1 - r;  // position of my row in sweep order
     constexpr int PG = (MODE == 0) ? 4 : MODE;  // rows per coupling group
@@ -208,6 +208,10 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
     const int ibase = FWD ? 0 : ((N + RS - 1) & ~(RS - 1));
     double ynext = 0.0;
     if (!FWD && j < N) ynext = C.x[(int64_t)(N - 1 - j) * W + r];
+    // stage / barrier phase of the group my block sits in, advanced incrementally (no division per block)
+    int gcur = (FWD ? 0 : C.NG) + j / G;
+    int s = gcur % C.NS;
+    unsigned ph = (unsigned)(gcur / C.NS) & 1u;
 
     for (int i = j; i < N; i += QW) {
         const int b = FWD ? i : N - 1 - i;
@@ -215,19 +219,18 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
         if (!FWD && i + QW < N) ynext = C.x[(int64_t)(N - 1 - (i + QW)) * W + r];
 
         Q32_T(t0);
-        const int g = i / G, mo = i % G;
-        const int gseq = (FWD ? 0 : C.NG) + g;
-        const int s = gseq % C.NS;
-        mbar_wait_guard(&C.full[s], (unsigned)(gseq / C.NS) & 1u, FWD ? "cons full fwd" : "cons full bwd", i, s, gseq);
+        const int mo = i % G;
+        mbar_wait_guard(&C.full[s], ph, FWD ? "cons full fwd" : "cons full bwd", i, s, gcur);
         Q32_T(t1);
         const int m = FWD ? mo : G - 1 - mo;  // slot of my block inside the group
         const unsigned char *st = C.stages + (size_t)s * GL.bytes;
         const double *Ls = reinterpret_cast<const double *>(st + (size_t)m * GL.blk_bytes);
-        // my row; the other triangle (and the diagonal) reads as zero
+        // my row.  The shuffle variant needs the other triangle (and the diagonal) to read as zero; the lean chain
+        // does not care: a finished lane's accumulator is dead, its value is read back from the ring at the end.
         double l[W];
 #pragma unroll
         for (int k = 0; k < W; ++k) {
-            const bool mine = FWD ? (k < r) : (k > r);
+            const bool mine = (MODE != 0) || (FWD ? (k < r) : (k > r));
             l[k] = mine ? Ls[k * ld + r] : 0.0;
         }
         const int ci = reinterpret_cast<const int *>(st + GL.o_cbr)[m * W + r];
@@ -259,6 +262,15 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
             // missing ones so that the stage's "empty" barrier (G arrivals) still completes
             const int extra = (i == N - 1) ? (G - 1 - mo) : 0;
             for (int e = 0; e <= extra; ++e) mbar_arrive(&C.empty[s]);
+        }
+        {
+            const int gn = (FWD ? 0 : C.NG) + (i + QW) / G;
+            s += gn - gcur;
+            gcur = gn;
+            while (s >= C.NS) {
+                s -= C.NS;
+                ph ^= 1u;
+            }
         }
         Q32_T(t2);
 
@@ -381,7 +393,7 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
 #undef LN
 #undef CF
         Q32_T(t4);
-        C.x[(int64_t)b * W + r] = acc;
+        C.x[(int64_t)b * W + r] = (MODE == 0) ? acc : ld_volatile_s(myslot);
         Q32_T(t5);
         Q32_ADD(0, t0, t1);
         Q32_ADD(1, t1, t2);
@@ -392,7 +404,7 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
     }
 }
 
-template <int ND, int MODE>
+template <int ND, int MODE, bool LD32>
 __global__ void __launch_bounds__((QW + NP) * 32, 1)
 solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                     const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
@@ -442,7 +454,7 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
 
     int nan_first = 0x7fffffff, zero_last = -1;
     if (warp >= QW) produce<true, ND>(C, warp - QW, lane);
-    else consume<true, ND, MODE>(C, warp, lane, nan_first, zero_last);
+    else consume<true, ND, MODE, LD32>(C, warp, lane, nan_first, zero_last);
     __syncthreads();  // y (in the x buffer) is complete and visible to the whole CTA
     ring_reset(C, tid, blockDim.x, ND);
     // "started" barriers keep counting phases across the sweeps: slots that saw one block fewer in the forward sweep
@@ -451,7 +463,7 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     if (tid < RS && (N & (RS - 1)) != 0 && tid >= (N & (RS - 1))) mbar_arrive(&C.started[tid]);
     __syncthreads();
     if (warp >= QW) produce<false, ND>(C, warp - QW, lane);
-    else consume<false, ND, MODE>(C, warp, lane, nan_first, zero_last);
+    else consume<false, ND, MODE, LD32>(C, warp, lane, nan_first, zero_last);
     if (warp < QW) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -472,24 +484,24 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
 
 // BDILU_QUAD_DBG (read once): timing experiments only (every variant gives correct results).
 //   2 = one producer warp, 4 = one bulk copy per block instead of per group,
-//   32 / 64 / 128 = chain variant: shuffle quads (32), lean chain merging the coupling every 4 rows (64) or every
-//   row (128); default: lean chain, every 2 rows (the fastest on B200, see profiles/)
+//   32 / 64 / 128 (builds with -DBDILU_QUAD_VARIANTS only) = chain variant: shuffle quads (32), lean chain merging
+//   the coupling every 4 rows (64) or every row (128); default: lean chain, every 2 rows (the fastest on B200)
 static int debug_switches()
 {
     static const int v = getenv("BDILU_QUAD_DBG") ? atoi(getenv("BDILU_QUAD_DBG")) : 0;
     return v;
 }
 
-template <int ND, int MODE>
-static cudaError_t launch_mode(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
-                               const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
-                               const VecLayout &V, int *flags)
+template <int ND, int MODE, bool LD32>
+static cudaError_t launch_one(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
+                              const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
+                              const VecLayout &V, int *flags)
 {
-    cudaError_t e = cudaFuncSetAttribute(solve_quad32_kernel<ND, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(solve_quad32_kernel<ND, MODE, LD32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          227 * 1024);
     if (e != cudaSuccess) return e;
-    solve_quad32_kernel<ND, MODE><<<nvec, (QW + NP) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V,
-                                                                      flags, NS, debug_switches());
+    solve_quad32_kernel<ND, MODE, LD32><<<nvec, (QW + NP) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x,
+                                                                            V, flags, NS, debug_switches());
     return cudaGetLastError();
 }
 
@@ -498,11 +510,16 @@ static cudaError_t launch_nd(unsigned nvec, size_t smem, int NS, cudaStream_t st
                              const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
                              const VecLayout &V, int *flags)
 {
+#define Q32_ARGS nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags
+#ifdef BDILU_QUAD_VARIANTS  // the other chain variants, for timing comparisons (BDILU_QUAD_DBG = 32 / 64 / 128)
     const int dbg = debug_switches();
-    if (dbg & 32) return launch_mode<ND, 0>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
-    if (dbg & 128) return launch_mode<ND, 1>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
-    if (dbg & 64) return launch_mode<ND, 4>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
-    return launch_mode<ND, 2>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags);
+    if (dbg & 32) return launch_one<ND, 0, false>(Q32_ARGS);
+    if (dbg & 64) return launch_one<ND, 4, false>(Q32_ARGS);
+    if (dbg & 128) return launch_one<ND, 1, false>(Q32_ARGS);
+#endif
+    if (D.ld == W) return launch_one<ND, 2, true>(Q32_ARGS);
+    return launch_one<ND, 2, false>(Q32_ARGS);
+#undef Q32_ARGS
 }
 
 }  // namespace quad
