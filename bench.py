@@ -60,6 +60,14 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def host_threads():
+    """Every host core this process may run on.  Not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def ncu_traffic(kernel, nsys):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
     capture of this workload (profiles/traffic.json, written by tools/ncu_traffic.py); None when there is none or
@@ -127,8 +135,7 @@ def run_reference(args, rank, world):
     from block_diag_ilu_b200 import synth
     w, N, d, nsys, nrhs = WORKLOADS[args.workload]
     orc = loader.best()
-    cores = os.cpu_count() or 1
-    threads = orc.max_threads() if hasattr(orc, "max_threads") else cores
+    threads = host_threads()
     # bounded sample: one system per host thread (at least 8), at most the full batch; cfg3 costs about
     # 0.11 s of one core per system, so K+W = 13 steps stay well under a minute of wall time.
     ns = min(nsys, max(8, threads))
@@ -163,7 +170,7 @@ def cpu_baseline_leg(w, N, d, nsys, nrhs, host_data, host_b):
     import numpy as np
     from oracle import loader
     orc = loader.best()
-    threads = orc.max_threads() if hasattr(orc, "max_threads") else (os.cpu_count() or 1)
+    threads = host_threads()
     ns = min(nsys, max(8, threads))
     nr = min(nrhs, 8)
     work = np.ascontiguousarray(host_data[:ns]).copy()

@@ -230,6 +230,8 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     constexpr int BPW = 32 / G;
     // pivot-row mailbox: [warp][group][2 buffers][WP doubles + reciprocal of the pivot (+ pad)]
     __shared__ __align__(16) double urow_s[FACTOR_WARPS][BPW][2][WP + 2];
+    // (U[k][k], 1/U[k][k]) of every step, left by the pivot lanes for the lanes that scale column k of sub/bot
+    __shared__ __align__(16) double2 diag_s[FACTOR_WARPS][BPW][WP];
 
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const int grp = lane / G, r = lane % G;
@@ -254,10 +256,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     int pos = r;          // current position of my row in the swapped ordering
     bool active = true;   // not yet chosen as a pivot row (padded rows take part: see above)
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
-    double my_diag = 1.0; // lane k keeps U[k][k]
-    double my_rinv = 1.0; // ... and its correctly rounded reciprocal
-    int my_info = 0;
-    bool weird = false;
+    double2 *dgs = diag_s[wic][grp];
 
 #pragma unroll
     for (int k = 0; k < WP; ++k) {
@@ -282,6 +281,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
 #pragma unroll
             for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
             ub[WP] = myrcp;
+            dgs[k] = make_double2(a[k], myrcp);
         }
         __syncwarp();
         const double2 *u2 = reinterpret_cast<const double2 *>(ub);
@@ -293,11 +293,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
             u[2 * m + 1] = t.y;
         }
         const double piv = u[k], rinv = ub[WP];
-        const int ehi = (__double2hiint(piv) >> 20) & 0x7ff;
-        const bool nz = (piv != 0.0);
-        weird |= nz && (ehi < 0x020 || ehi > 0x7dd);
-        if (r == k) { my_diag = piv; my_rinv = rinv; }
-        if (!nz && my_info == 0) my_info = k + 1;  // dgetf2: record, leave the column unscaled
+        const bool nz = (piv != 0.0);  // dgetf2 leaves the column of an exactly zero pivot unscaled (info, below)
 
         // ---- multiplier by (exactly rounded) division, rank-1 update of the trailing columns ----
         double l = a[k] * rinv;
@@ -309,6 +305,16 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
         for (int j = k + 1; j < WP; ++j) a[j] = fma(-l, u[j], a[j]);
     }
 
+    // lane k picks up U[k][k] and its reciprocal; the per-block bookkeeping happens once, here, not in every step:
+    // pivots outside the exact range of the reciprocal send the warp to the slow path, the first exactly zero
+    // pivot is dgetrf's info (1-based).
+    __syncwarp();
+    const double2 dd = dgs[r];
+    const double my_diag = dd.x, my_rinv = dd.y;
+    const bool weird = (my_diag != 0.0) && !rcp_fast_ok(my_diag);
+    const unsigned zb = __ballot_sync(FULL, my_diag == 0.0);
+    const unsigned zg = (G == 32) ? zb : ((zb >> (grp * G)) & ((1u << (G & 31)) - 1u));
+    const int my_info = zg ? __ffs(zg) : 0;
     if (__any_sync(FULL, weird)) {
         // rare: redo this warp's blocks with true divisions from the pristine data (nothing stored yet)
         factor_block_slow<WP>(sysdata, blk, D, w, ld, sys, bi, r, live, urow[0], ipiv, rowbycol, colbyrow, info);
