@@ -19,6 +19,10 @@
 namespace bdilu {
 
 constexpr int FACTOR_WARPS = 4;
+#ifndef BDILU_FACTOR_SHFL_ROW
+#define BDILU_FACTOR_SHFL_ROW 0
+#endif
+constexpr bool SHFL_ROW = BDILU_FACTOR_SHFL_ROW != 0;  // blockw 32: pivot row by shuffle (1: 3.45 ms on cfg3) or mailbox (0: 3.2 ms)
 
 // argmax of v over the group with ties broken towards the lowest `pos`; returns the winning lane
 // (group-local index).  Inactive lanes pass v = -1.
@@ -274,25 +278,37 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
         if (pos == k) pos = (int)q;
         if (is_p) { pos = k; active = false; }
 
-        // ---- publish the pivot row (columns k..WP-1) and 1/pivot to the group ----
-        double *ub = urow[k & 1];
-        if (is_p) {
-            double2 *u2w = reinterpret_cast<double2 *>(ub);
-#pragma unroll
-            for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
-            ub[WP] = myrcp;
-            dgs[k] = make_double2(a[k], myrcp);
-        }
-        __syncwarp();
-        const double2 *u2 = reinterpret_cast<const double2 *>(ub);
+        // ---- hand the pivot row (columns k..WP-1) and 1/pivot to the group ----
         double u[WP];
+        double rinv;
+        if (G == 32 && SHFL_ROW) {
+            // by shuffle from the pivot lane: no shared-memory store.  (The store of a whole row by ONE lane pays
+            // the operand transfer of all 32 lanes; ncu showed the register -> MIO path 78 % busy with it.)
+            const int pl = __ffs(__ballot_sync(FULL, is_p)) - 1;
 #pragma unroll
-        for (int m = k / 2; m < WP / 2; ++m) {
-            const double2 t = u2[m];
-            u[2 * m] = t.x;
-            u[2 * m + 1] = t.y;
+            for (int j = k; j < WP; ++j) u[j] = group_bcast<32>(a[j], pl);
+            rinv = group_bcast<32>(myrcp, pl);
+            if (is_p) dgs[k] = make_double2(a[k], myrcp);
+        } else {
+            double *ub = urow[k & 1];
+            if (is_p) {
+                double2 *u2w = reinterpret_cast<double2 *>(ub);
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) u2w[m] = make_double2(a[2 * m], a[2 * m + 1]);
+                ub[WP] = myrcp;
+                dgs[k] = make_double2(a[k], myrcp);
+            }
+            __syncwarp();
+            const double2 *u2 = reinterpret_cast<const double2 *>(ub);
+#pragma unroll
+            for (int m = k / 2; m < WP / 2; ++m) {
+                const double2 t = u2[m];
+                u[2 * m] = t.x;
+                u[2 * m + 1] = t.y;
+            }
+            rinv = ub[WP];
         }
-        const double piv = u[k], rinv = ub[WP];
+        const double piv = u[k];
         const bool nz = (piv != 0.0);  // dgetf2 leaves the column of an exactly zero pivot unscaled (info, below)
 
         // ---- multiplier by (exactly rounded) division, rank-1 update of the trailing columns ----
