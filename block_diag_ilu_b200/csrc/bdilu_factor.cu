@@ -22,6 +22,10 @@ constexpr int FACTOR_WARPS = 4;
 #ifndef BDILU_FACTOR_SHFL_ROW
 #define BDILU_FACTOR_SHFL_ROW 0
 #endif
+#ifndef BDILU_FACTOR_PAIRED
+#define BDILU_FACTOR_PAIRED 1
+#endif
+constexpr bool PAIRED = BDILU_FACTOR_PAIRED != 0;  // blockw 32: two elimination steps per pivot-row publication
 constexpr bool SHFL_ROW = BDILU_FACTOR_SHFL_ROW != 0;  // blockw 32: pivot row by shuffle (1: 3.45 ms on cfg3) or mailbox (0: 3.2 ms)
 
 // argmax of v over the group with ties broken towards the lowest `pos`; returns the winning lane
@@ -93,6 +97,14 @@ __device__ __forceinline__ unsigned group_min_u(unsigned v)
 #pragma unroll
     for (int off = G / 2; off > 0; off >>= 1) v = min(v, __shfl_xor_sync(FULL, v, off, G));
     return v;
+}
+
+// 16-byte shared-memory store under a predicate (never a branch: see the paired loop of factor_kernel)
+__device__ __forceinline__ void sts128_if(bool p, unsigned saddr, double x, double y)
+{
+    asm volatile("{ .reg .pred p; setp.ne.u32 p, %3, 0; @p st.shared.v2.f64 [%0], {%1, %2}; }" ::"r"(saddr), "d"(x),
+                 "d"(y), "r"((unsigned)p)
+                 : "memory");
 }
 
 // Slow path (true divisions, branches): the algorithm exactly as documented at the top of this file.
@@ -262,6 +274,98 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
     double2 *dgs = diag_s[wic][grp];
 
+    if constexpr (G == 32 && PAIRED && !SHFL_ROW) {
+        // ---- two elimination steps per publication (blockw 32) --------------------------------------------------
+        // A shared-memory store costs the register->MIO transfer of all 32 lanes whatever the number of active ones
+        // (measured: STS.128 4.2 SM-cycles with 1 or 32 lanes, scratch/bw/mio_bench.cu), and that path bounds this
+        // kernel.  So the pivot rows of steps k and k+1 go out in ONE store sequence, two lanes active:
+        //   step k   : its pivot lane publishes only (pivot, 1/pivot, u0[k+1]); everybody forms l0 and updates
+        //              column k+1 alone, which is all the search of step k+1 needs;
+        //   step k+1 : its pivot lane publishes its row as it stands, i.e. WITHOUT step k's update in columns
+        //              > k+1, together with the finished row of step k; every lane redoes that one update itself,
+        //              u1[c] = r1[c] - l0(q1)*u0[c] (the same fma the pivot lane would have done), and then applies
+        //              both rank-1 updates in the order of the serial algorithm.  Results are bit-identical.
+        double2 *ub0 = reinterpret_cast<double2 *>(urow[0]);
+        double2 *ub1 = reinterpret_cast<double2 *>(urow[1]);
+        double *nx = &urow[0][WP];  // u0[k+1]
+        const unsigned ub0_s = (unsigned)__cvta_generic_to_shared(ub0), ub1_s = (unsigned)__cvta_generic_to_shared(ub1);
+#pragma unroll
+        for (int k = 0; k < WP; k += 2) {
+            // ---- step k: search, then the three numbers column k+1 needs ----
+            const int hi0 = active ? (__double2hiint(a[k]) & 0x7fffffff) : -1;
+            const unsigned lo0 = (unsigned)__double2loint(a[k]);
+            const double rcp0 = rcp_fast(a[k]);  // speculative; only the winner's is used
+            const int mhi0 = group_max_i<G>(hi0);
+            const bool c10 = (hi0 == mhi0);
+            const unsigned mlo0 = group_max_u<G>(c10 ? lo0 : 0u);
+            const bool c20 = c10 && (lo0 == mlo0);
+            const unsigned q0 = group_min_u<G>(c20 ? (unsigned)pos : 0xffffu);
+            const bool isp0 = c20 && ((unsigned)pos == q0);
+            if (r == k) my_ipiv = (int)q0 + 1;
+            if (pos == k) pos = (int)q0;
+            if (isp0) {
+                pos = k;
+                active = false;
+                dgs[k] = make_double2(a[k], rcp0);
+                *nx = a[k + 1];
+            }
+            __syncwarp();
+            const double2 d0 = dgs[k];
+            const double u0n = *nx;
+            const double piv0 = d0.x, rinv0 = d0.y;
+            const bool nz0 = (piv0 != 0.0);  // dgetf2 leaves the column of an exactly zero pivot unscaled
+            double l0 = a[k] * rinv0;
+            l0 = fma(fma(-l0, piv0, a[k]), rinv0, l0);
+            const bool upd0 = active && nz0;
+            a[k] = upd0 ? l0 : a[k];
+            l0 = upd0 ? l0 : 0.0;
+            a[k + 1] = fma(-l0, u0n, a[k + 1]);
+
+            // ---- step k+1: search on the updated column ----
+            const int hi1 = active ? (__double2hiint(a[k + 1]) & 0x7fffffff) : -1;
+            const unsigned lo1 = (unsigned)__double2loint(a[k + 1]);
+            const double rcp1 = rcp_fast(a[k + 1]);
+            const int mhi1 = group_max_i<G>(hi1);
+            const bool c11 = (hi1 == mhi1);
+            const unsigned mlo1 = group_max_u<G>(c11 ? lo1 : 0u);
+            const bool c21 = c11 && (lo1 == mlo1);
+            const unsigned q1 = group_min_u<G>(c21 ? (unsigned)pos : 0xffffu);
+            const bool isp1 = c21 && ((unsigned)pos == q1);
+            if (r == k + 1) my_ipiv = (int)q1 + 1;
+            if (pos == k + 1) pos = (int)q1;
+            if (isp1) {
+                pos = k + 1;
+                active = false;
+                dgs[k + 1] = make_double2(a[k + 1], rcp1);
+            }
+            // ---- both pivot rows, columns k.. (the pair (k, k+1) of row q1 carries l0(q1) and the pivot) ----
+            {
+                // ONE predicated store per column pair, executed by both pivot lanes at once (a branch here makes
+                // ptxas emit one store sequence per lane, which is what this loop exists to avoid)
+                const bool pub = isp0 || isp1;
+                const unsigned ubw = isp1 ? ub1_s : ub0_s;
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) sts128_if(pub, ubw + 16u * m, a[2 * m], a[2 * m + 1]);
+            }
+            __syncwarp();
+            const double2 hd = ub1[k / 2];
+            const double l0q = nz0 ? hd.x : 0.0;  // row q1 was active in step k: its a[k] is its multiplier unless !nz0
+            const double piv1 = hd.y, rinv1 = dgs[k + 1].y;
+            const bool nz1 = (piv1 != 0.0);
+            double l1 = a[k + 1] * rinv1;
+            l1 = fma(fma(-l1, piv1, a[k + 1]), rinv1, l1);
+            const bool upd1 = active && nz1;
+            a[k + 1] = upd1 ? l1 : a[k + 1];
+            l1 = upd1 ? l1 : 0.0;
+#pragma unroll
+            for (int m = k / 2 + 1; m < WP / 2; ++m) {
+                const double2 t0 = ub0[m], t1 = ub1[m];
+                const double u1x = fma(-l0q, t0.x, t1.x), u1y = fma(-l0q, t0.y, t1.y);
+                a[2 * m] = fma(-l1, u1x, fma(-l0, t0.x, a[2 * m]));
+                a[2 * m + 1] = fma(-l1, u1y, fma(-l0, t0.y, a[2 * m + 1]));
+            }
+        }
+    } else {
 #pragma unroll
     for (int k = 0; k < WP; ++k) {
         // ---- pivot search (idamax over the not-yet-chosen rows, ties -> lowest current position) ----
@@ -319,6 +423,7 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
         l = upd ? l : 0.0;
 #pragma unroll
         for (int j = k + 1; j < WP; ++j) a[j] = fma(-l, u[j], a[j]);
+    }
     }
 
     // lane k picks up U[k][k] and its reciprocal; the per-block bookkeeping happens once, here, not in every step:
