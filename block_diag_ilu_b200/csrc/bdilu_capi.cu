@@ -188,7 +188,22 @@ int bdilu_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int
     if (rc) return rc;
     if (nsys == 0) return BDILU_OK;
     if (!dst || !src) return fail(BDILU_ERR_ARG, "null pointer");
-    CU(launch_scale_diag_add(dst, src, sys_stride, nsys, D, scale, diag_add, (cudaStream_t)stream));
+    CU(launch_scale_diag_add(dst, src, sys_stride, sys_stride, nsys, D, scale, diag_add, (cudaStream_t)stream));
+    return BDILU_OK;
+}
+
+int bdilu_factor_scaled(double *dst, int64_t dst_stride, const double *src, int64_t src_stride, int nsys, int nblocks,
+                        int blockw, int ndiag, int nsat, int ld, double scale, double diag_add, int *ipiv,
+                        int *rowbycol, int *colbyrow, int *info, void *stream)
+{
+    Dims D;
+    int rc = check_dims(nsys, dst_stride, nblocks, blockw, ndiag, nsat, ld, D);
+    if (rc) return rc;
+    if (nsys > 1 && src_stride < D.ndata) return fail(BDILU_ERR_ARG, "src_stride < ndata");
+    if (nsys == 0) return BDILU_OK;
+    if (!dst || !src || !ipiv || !rowbycol || !colbyrow || !info) return fail(BDILU_ERR_ARG, "null pointer");
+    CU(launch_factor_scaled(dst, dst_stride, src, src_stride, nsys, D, scale, diag_add, ipiv, rowbycol, colbyrow, info,
+                            (cudaStream_t)stream));
     return BDILU_OK;
 }
 

@@ -116,11 +116,35 @@ struct RowState {
     bool fast;
 };
 
+// Where the unfactored numbers of one system come from.  In place (`scaled` false): the destination itself.  Fused
+// assembly of M = scale*J + diag_add*I (BlockDiagMatrix::scale_diag_add, block_diag_ilu.hpp:276-287, the step an
+// integrator runs before every factorisation): J is read from `sys`, scaled on the fly -- product and sum rounded
+// separately, like the reference's two statements -- and only the factors are ever written.
+struct SrcView {
+    const double *sys;
+    double scale, diag_add;
+    bool scaled;
+    __device__ __forceinline__ double at(int64_t off) const
+    {
+        const double v = sys[off];
+        return scaled ? __dmul_rn(scale, v) : v;
+    }
+    __device__ __forceinline__ double block_at(int64_t off, bool on_diag) const
+    {
+        double v = ld_stream(sys + off);
+        if (scaled) {
+            v = __dmul_rn(scale, v);
+            if (on_diag) v = __dadd_rn(v, diag_add);
+        }
+        return v;
+    }
+};
+
 // Stores what one lane owns after the elimination: its row of L\U at row `pos`, the permutation
 // vectors, the scaled sub/bot entries of column r, and the block's info.
 template <int WP>
-__device__ __forceinline__ void store_block(const double (&a)[WP], const RowState &S, double *sysdata, double *blk,
-                                            const Dims &D, int w, int ld, int sys, int bi, int r,
+__device__ __forceinline__ void store_block(const double (&a)[WP], const RowState &S, const SrcView &V, double *sysdata,
+                                            double *blk, const Dims &D, int w, int ld, int sys, int bi, int r,
                                             int *__restrict__ ipiv, int *__restrict__ rowbycol,
                                             int *__restrict__ colbyrow, int *__restrict__ info)
 {
@@ -132,7 +156,7 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
     double sv[PF];
 #pragma unroll
     for (int di = 0; di < PF; ++di)
-        sv[di] = (di < nsub) ? sysdata[D.off_sub + D.diag_chunk(di, bi) + r] : 0.0;
+        sv[di] = (di < nsub) ? V.at(D.off_sub + D.diag_chunk(di, bi) + r) : 0.0;
 #pragma unroll
     for (int c = 0; c < WP; ++c)
         if (c < w) blk[(int64_t)c * ld + S.pos] = a[c];
@@ -150,15 +174,28 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
     for (int di = 0; di < PF; ++di)
         if (di < nsub) sysdata[D.off_sub + D.diag_chunk(di, bi) + r] = quot(sv[di]);
     for (int di = PF; di < nsub; ++di) {
-        double *sp = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
-        *sp = quot(*sp);
+        const int64_t off = D.off_sub + D.diag_chunk(di, bi) + r;
+        sysdata[off] = quot(V.at(off));
     }
     // bot(sati,bi,c) /= U[c][c]  (:476-479)
     if (bi < D.nsat)
         for (int sati = bi; sati < D.nsat; ++sati) {
-            double *sp = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
-            *sp = *sp / S.diag;
+            const int64_t off = D.off_bot + D.sat_chunk(sati, bi) + r;
+            sysdata[off] = V.at(off) / S.diag;
         }
+    if (V.scaled) {
+        // sup and top are not touched by the factorisation; the fused assembly still owes the destination their
+        // scaled copies (same index sets as sub and bot)
+        for (int di = 0; di < nsub; ++di) {
+            const int64_t off = D.off_sup + D.diag_chunk(di, bi) + r;
+            sysdata[off] = V.at(off);
+        }
+        if (bi < D.nsat)
+            for (int sati = bi; sati < D.nsat; ++sati) {
+                const int64_t off = D.off_top + D.sat_chunk(sati, bi) + r;
+                sysdata[off] = V.at(off);
+            }
+    }
     if (S.info != 0 && r == 0) {
         // keep the failing block with the lowest index (serial loop order, :469-470)
         const int key = (bi << 7) | S.info;
@@ -175,8 +212,8 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
 // top of this file, from the pristine block in global memory.  Taken only by warps that met a pivot
 // outside the fast reciprocal's exact range.
 template <int WP>
-__device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dims D, int w, int ld, int sys, int bi,
-                                               int r, bool live, double *ubuf, int *__restrict__ ipiv,
+__device__ __noinline__ void factor_block_slow(SrcView V, double *sysdata, double *blk, Dims D, int w, int ld, int sys,
+                                               int bi, int r, bool live, double *ubuf, int *__restrict__ ipiv,
                                                int *__restrict__ rowbycol, int *__restrict__ colbyrow,
                                                int *__restrict__ info)
 {
@@ -184,7 +221,7 @@ __device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dim
     const bool rowok = r < w;
     double a[WP];
     for (int c = 0; c < WP; ++c)
-        a[c] = (rowok && c < w) ? blk[(int64_t)c * ld + r] : ((c == r) ? 1.0 : 0.0);
+        a[c] = (rowok && c < w) ? V.block_at(D.block(bi) + (int64_t)c * ld + r, c == r) : ((c == r) ? 1.0 : 0.0);
     RowState S;
     S.pos = r; S.ipiv = r + 1; S.info = 0; S.diag = 1.0; S.rinv = 1.0; S.fast = false;
     bool active = rowok;
@@ -216,13 +253,15 @@ __device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dim
         rowbycol[ib + S.pos] = r;
         colbyrow[ib + r] = S.pos;
         for (int di = 0; di < D.ndiag && bi + di < D.nblocks - 1; ++di) {
-            double *s = sysdata + D.off_sub + D.diag_chunk(di, bi) + r;
-            *s = *s / S.diag;
+            const int64_t off = D.off_sub + D.diag_chunk(di, bi) + r;
+            sysdata[off] = V.at(off) / S.diag;
+            if (V.scaled) sysdata[off - D.off_sub + D.off_sup] = V.at(off - D.off_sub + D.off_sup);
         }
         if (bi < D.nsat)
             for (int sati = bi; sati < D.nsat; ++sati) {
-                double *s = sysdata + D.off_bot + D.sat_chunk(sati, bi) + r;
-                *s = *s / S.diag;
+                const int64_t off = D.off_bot + D.sat_chunk(sati, bi) + r;
+                sysdata[off] = V.at(off) / S.diag;
+                if (V.scaled) sysdata[off - D.off_bot + D.off_top] = V.at(off - D.off_bot + D.off_top);
             }
         if (S.info != 0 && r == 0) {
             const int key = (bi << 7) | S.info;
@@ -236,11 +275,17 @@ __device__ __noinline__ void factor_block_slow(double *sysdata, double *blk, Dim
     }
 }
 
-template <int WP, bool EXACT>
+// the source of a fused assembly (SCALED kernels only): J, its system stride, and M = scale*J + diag_add*I
+struct ScaledSrc {
+    const double *src;
+    int64_t sys_stride;
+    double scale, diag_add;
+};
+
+template <int WP, bool EXACT, bool SCALED>
 __global__ void __launch_bounds__(FACTOR_WARPS * 32, WP == 32 ? 4 : 6)
-factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
-              int *__restrict__ ipiv, int *__restrict__ rowbycol, int *__restrict__ colbyrow,
-              int *__restrict__ info)
+factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restrict__ ipiv,
+              int *__restrict__ rowbycol, int *__restrict__ colbyrow, int *__restrict__ info, ScaledSrc SS)
 {
     constexpr int G = WP;
     constexpr int BPW = 32 / G;
@@ -260,13 +305,16 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     double *sysdata = data + (int64_t)sys * sys_stride;
     double *blk = sysdata + D.block(bi);
     const bool rowok = r < w;
+    SrcView V;
+    V.sys = SCALED ? SS.src + (int64_t)sys * SS.sys_stride : sysdata;
+    V.scale = SS.scale; V.diag_add = SS.diag_add; V.scaled = SCALED;
 
     // row r of the block; rows/columns beyond w are padded with the identity (they pivot on themselves
     // in the trailing steps k >= w and never disturb the real rows)
     double a[WP];
 #pragma unroll
     for (int c = 0; c < WP; ++c)
-        a[c] = (rowok && c < w) ? ld_stream(blk + (int64_t)c * ld + r) : ((c == r) ? 1.0 : 0.0);
+        a[c] = (rowok && c < w) ? V.block_at(D.block(bi) + (int64_t)c * ld + r, c == r) : ((c == r) ? 1.0 : 0.0);
 
     double (*urow)[WP + 2] = urow_s[wic][grp];
     int pos = r;          // current position of my row in the swapped ordering
@@ -438,13 +486,13 @@ factor_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
     const int my_info = zg ? __ffs(zg) : 0;
     if (__any_sync(FULL, weird)) {
         // rare: redo this warp's blocks with true divisions from the pristine data (nothing stored yet)
-        factor_block_slow<WP>(sysdata, blk, D, w, ld, sys, bi, r, live, urow[0], ipiv, rowbycol, colbyrow, info);
+        factor_block_slow<WP>(V, sysdata, blk, D, w, ld, sys, bi, r, live, urow[0], ipiv, rowbycol, colbyrow, info);
         return;
     }
     if (live && rowok) {
         RowState S;
         S.pos = pos; S.ipiv = my_ipiv; S.info = my_info; S.diag = my_diag; S.rinv = my_rinv; S.fast = true;
-        store_block<WP>(a, S, sysdata, blk, D, w, ld, sys, bi, r, ipiv, rowbycol, colbyrow, info);
+        store_block<WP>(a, S, V, sysdata, blk, D, w, ld, sys, bi, r, ipiv, rowbycol, colbyrow, info);
     }
 }
 
@@ -549,23 +597,23 @@ factor_wide_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims
     }
 }
 
-cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
-                          int *rowbycol, int *colbyrow, int *info, cudaStream_t st)
+// src == nullptr: in place.  Otherwise the fused assembly data = LU(scale*src + diag_add*I) (src may equal data).
+static cudaError_t launch_factor_any(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv, int *rowbycol,
+                                     int *colbyrow, int *info, const ScaledSrc &SS, cudaStream_t st)
 {
     const int64_t total = (int64_t)nsys * D.nblocks;
     if (total == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int) * (size_t)nsys, st);
     if (e != cudaSuccess) return e;
-#define BDILU_LAUNCH_FACTOR(WP)                                                                    \
-    {                                                                                              \
-        const int64_t per_cta = (int64_t)FACTOR_WARPS * (32 / WP);                                 \
-        const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);                         \
-        if (D.w == WP && D.ld == WP)                                                               \
-            factor_kernel<WP, true><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, \
-                                                                        rowbycol, colbyrow, info);  \
-        else                                                                                       \
-            factor_kernel<WP, false><<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, \
-                                                                         rowbycol, colbyrow, info); \
+    const bool scaled = SS.src != nullptr;
+#define BDILU_LAUNCH_FACTOR(WP)                                                                                    \
+    {                                                                                                              \
+        const int64_t per_cta = (int64_t)FACTOR_WARPS * (32 / WP);                                                 \
+        const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);                                         \
+        const bool exact = (D.w == WP && D.ld == WP);                                                              \
+        auto kern = scaled ? (exact ? factor_kernel<WP, true, true> : factor_kernel<WP, false, true>)              \
+                           : (exact ? factor_kernel<WP, true, false> : factor_kernel<WP, false, false>);           \
+        kern<<<grid, FACTOR_WARPS * 32, 0, st>>>(data, sys_stride, nsys, D, ipiv, rowbycol, colbyrow, info, SS);   \
     }
     const int w = D.w;
     if (w <= 2) BDILU_LAUNCH_FACTOR(2)
@@ -573,11 +621,32 @@ cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims
     else if (w <= 8) BDILU_LAUNCH_FACTOR(8)
     else if (w <= 16) BDILU_LAUNCH_FACTOR(16)
     else if (w <= 32) BDILU_LAUNCH_FACTOR(32)
-    else factor_wide_kernel<<<(unsigned)total, 64, 0, st>>>(data, sys_stride, nsys, D, ipiv, rowbycol,
-                                                             colbyrow, info);
+    else {
+        // 32 < blockw: no fused load in the wide kernel; assemble with the streaming kernel first
+        if (scaled) {
+            e = launch_scale_diag_add(data, SS.src, sys_stride, SS.sys_stride, nsys, D, SS.scale, SS.diag_add, st);
+            if (e != cudaSuccess) return e;
+        }
+        factor_wide_kernel<<<(unsigned)total, 64, 0, st>>>(data, sys_stride, nsys, D, ipiv, rowbycol, colbyrow, info);
+    }
 #undef BDILU_LAUNCH_FACTOR
     count_launch(1);
     return cudaGetLastError();
+}
+
+cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
+                          int *rowbycol, int *colbyrow, int *info, cudaStream_t st)
+{
+    const ScaledSrc none = {nullptr, 0, 1.0, 0.0};
+    return launch_factor_any(data, sys_stride, nsys, D, ipiv, rowbycol, colbyrow, info, none, st);
+}
+
+cudaError_t launch_factor_scaled(double *dst, int64_t dst_stride, const double *src, int64_t src_stride, int nsys,
+                                 const Dims &D, double scale, double diag_add, int *ipiv, int *rowbycol, int *colbyrow,
+                                 int *info, cudaStream_t st)
+{
+    const ScaledSrc SS = {src, src_stride, scale, diag_add};
+    return launch_factor_any(dst, dst_stride, nsys, D, ipiv, rowbycol, colbyrow, info, SS, st);
 }
 
 }  // namespace bdilu

@@ -43,7 +43,12 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
                                   const double *b, const double *x, const VecLayout &V, double *norm2,
                                   cudaStream_t st);
 
-cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int nsys,
+cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, int nsys,
                                   const Dims &D, double scale, double diag_add, cudaStream_t st);
+
+// dst = ILU factors of scale*src + diag_add*I, assembled in the factor kernel's load (blockw <= 32)
+cudaError_t launch_factor_scaled(double *dst, int64_t dst_stride, const double *src, int64_t src_stride, int nsys,
+                                 const Dims &D, double scale, double diag_add, int *ipiv, int *rowbycol, int *colbyrow,
+                                 int *info, cudaStream_t st);
 
 }  // namespace bdilu

@@ -71,20 +71,21 @@ matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const
 }
 
 __global__ void __launch_bounds__(256)
-scale_diag_add_kernel(double *__restrict__ dst, const double *__restrict__ src, int64_t sys_stride, Dims D,
+scale_diag_add_kernel(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, Dims D,
                       double scale, double diag_add)
 {
     const int sys = blockIdx.y;
-    const int64_t base = (int64_t)sys * sys_stride;
+    const int64_t base = (int64_t)sys * dst_stride, sbase = (int64_t)sys * src_stride;
     const int64_t blk_end = D.off_sub;
     const int64_t per_block = (int64_t)D.w * D.ld;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D.ndata;
          i += (int64_t)gridDim.x * blockDim.x) {
-        double v = scale * src[base + i];
+        // product and sum rounded separately, like the reference's two statements (no FMA contraction)
+        double v = __dmul_rn(scale, src[sbase + i]);
         if (i < blk_end) {
             const int64_t in_blk = i % per_block;
             const int c = (int)(in_blk / D.ld), r = (int)(in_blk % D.ld);
-            if (r == c) v += diag_add;
+            if (r == c) v = __dadd_rn(v, diag_add);
         }
         dst[base + i] = v;
     }
@@ -117,14 +118,14 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
     return cudaGetLastError();
 }
 
-cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int nsys,
+cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, int nsys,
                                   const Dims &D, double scale, double diag_add, cudaStream_t st)
 {
     if (nsys == 0 || D.ndata == 0) return cudaSuccess;
     if (nsys > 65535) return cudaErrorInvalidValue;
     const int64_t want = (D.ndata + 255) / 256;
     dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), nsys);
-    scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst, src, sys_stride, D, scale, diag_add);
+    scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst, src, dst_stride, src_stride, D, scale, diag_add);
     count_launch(1);
     return cudaGetLastError();
 }

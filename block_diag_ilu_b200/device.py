@@ -83,6 +83,38 @@ class BatchedILU:
         if check and bool((self.info != 0).any().item()):
             raise RuntimeError("ILU failed!")
 
+    @classmethod
+    def from_scaled(cls, src, scale, diag_add, nblocks, blockw, ndiag, nsat=0, ld=None, out=None, check=True):
+        """ILU of scale*src + diag_add*I, assembled inside the factor kernel's load (bdilu_factor_scaled).
+
+        The pair `m.set_to_eye_plus_scaled_mtx(-gamma, J); ILU_inplace(&m)` of an implicit integrator
+        (block_diag_ilu.hpp:276-290, 430-485) in one pass over the matrix: `src` (J) is only read, the factors
+        go to `out` (a new tensor by default; pass the previous factor storage to re-factor with a new gamma).
+        """
+        _lib.require_device()
+        self = cls.__new__(cls)
+        self.shape = Shape(nblocks, blockw, ndiag, nsat, ld)
+        src = _check_data(src, self.shape)
+        self.data = torch.empty_like(src) if out is None else _check_data(out, self.shape)
+        if self.data.shape[0] != src.shape[0]:
+            raise ValueError("out must hold as many systems as src")
+        self.nsys = src.shape[0]
+        dev, n = src.device, self.shape.n
+        self.ipiv = torch.empty((self.nsys, n), dtype=torch.int32, device=dev)
+        self.rowbycol = torch.empty_like(self.ipiv)
+        self.colbyrow = torch.empty_like(self.ipiv)
+        self.info = torch.empty((self.nsys,), dtype=torch.int32, device=dev)
+        self.flags = None
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().bdilu_factor_scaled(
+                _lib.ptr(self.data), self.data.stride(0), _lib.ptr(src), src.stride(0), self.nsys,
+                *self.shape.dims(), float(scale), float(diag_add),
+                _lib.ptr(self.ipiv), _lib.ptr(self.rowbycol), _lib.ptr(self.colbyrow), _lib.ptr(self.info),
+                _stream()))
+        if check and bool((self.info != 0).any().item()):
+            raise RuntimeError("ILU failed!")
+        return self
+
     def solve(self, b, out=None):
         """x with the shape of b; per-vector reference return codes land in self.flags [nsys, nrhs]."""
         b3, shp = _vec3(b, self.nsys, self.shape.n)

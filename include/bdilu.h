@@ -124,6 +124,19 @@ BDILU_API int bdilu_scale_diag_add(double *dst, const double *src, int64_t sys_s
                          int nblocks, int blockw, int ndiag, int nsat, int ld,
                          double scale, double diag_add, void *stream);
 
+/* Fused assembly + factorisation, the pair an implicit integrator runs at every Jacobian refresh
+ * (`m.set_to_eye_plus_scaled_mtx(-gamma, J); ILU_inplace ilu(&m);`, block_diag_ilu.hpp:276-290 + 430-485;
+ * caller external/anyode/include/anyode/anyode_iterative.hpp:58-62): dst receives the ILU factors of
+ * scale*src + diag_add*I.  src (the Jacobian, nsys systems src_stride doubles apart) is only read and stays
+ * valid for the next gamma; it is scaled inside the factor kernel's load, so the separate pass of
+ * bdilu_scale_diag_add over the matrix (one full read + write) disappears.  dst may equal src.  Results are
+ * identical to bdilu_scale_diag_add followed by bdilu_factor, except that padding elements of dst
+ * (rows >= blockw when ld > blockw) are left untouched.  Outputs as bdilu_factor. */
+BDILU_API int bdilu_factor_scaled(double *dst, int64_t dst_stride, const double *src, int64_t src_stride, int nsys,
+                        int nblocks, int blockw, int ndiag, int nsat, int ld,
+                        double scale, double diag_add,
+                        int *ipiv, int *rowbycol, int *colbyrow, int *info, void *stream);
+
 /* Scratch bytes the device entry points need from the caller: always 0 today (y stays on chip). */
 BDILU_API size_t bdilu_workspace_bytes(int nsys, int nblocks, int blockw, int ndiag, int nsat, int ld, int nrhs);
 
