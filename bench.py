@@ -75,7 +75,7 @@ def ncu_traffic(kernel, nsys):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        e = t["kernels"][kernel]
+        e = next(v for k, v in t["kernels"].items() if k.startswith(kernel))
         return float(e["dram_bytes"]) if int(e["nsys"]) == int(nsys) else None
     except Exception:
         return None
@@ -289,7 +289,7 @@ def run_ours(args, rank, world, local_rank):
     dom_ms = max(kf, ks)
     achieved = nsys * AB[dom] / (dom_ms * 1e-3) / 1e9
     fused_gbs = nsys * AB["fused"] / (ms_per_step * 1e-3) / 1e9
-    kname = "factor_kernel<32,1>" if dom == "factor" else "solve_quad32_kernel<2,2>"
+    kname = "factor_kernel<32,true,false>" if dom == "factor" else "solve_quad32_kernel<2,2,true>"
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(kname, nsys),
