@@ -23,7 +23,12 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
-extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel
+extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
+                          // 4 = many-vector kernel whenever the shape allows it, 5 = automatic without the many-vector kernel
+// many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
+bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
+                           const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
+                           cudaStream_t st, cudaError_t *err);
 bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                            cudaStream_t st, cudaError_t *err);

@@ -213,6 +213,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
     const int64_t total = (int64_t)nsys * V.nrhs;
     if (total == 0 || D.nblocks == 0) return cudaSuccess;
     cudaError_t werr;
+    if (try_launch_solve_mrhs(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr)) return werr;
     if (g_solve_path != 1 && try_launch_solve_wave(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr))
         return werr;
 #define BDILU_LAUNCH_SOLVE(WP)                                                                       \

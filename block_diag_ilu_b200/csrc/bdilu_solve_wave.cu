@@ -255,7 +255,7 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
         if (*err != cudaSuccess) return true;
         attr_set = true;
     }
-    if (w == 32 && g_solve_path == 0 &&
+    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5) &&
         try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err)) {
         count_launch(1);
         return true;

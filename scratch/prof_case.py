@@ -8,7 +8,8 @@ N = int(sys.argv[2]) if len(sys.argv) > 2 else 8192
 w = int(sys.argv[3]) if len(sys.argv) > 3 else 32
 d = int(sys.argv[4]) if len(sys.argv) > 4 else 2
 reps = int(sys.argv[5]) if len(sys.argv) > 5 else 2
-data, b = synth.make_batch_device(nsys, N, w, d, torch.device("cuda:0"), seed=5)
+nrhs = int(sys.argv[6]) if len(sys.argv) > 6 else 1
+data, b = synth.make_batch_device(nsys, N, w, d, torch.device("cuda:0"), seed=5, nrhs=nrhs)
 for _ in range(reps):
     work = data.clone()
     e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))

@@ -91,12 +91,16 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-@pytest.fixture(params=["auto", "chain", "wave_generic", "wave32_onerow"])
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4}
+
+
+@pytest.fixture(params=list(PATHS))
 def solve_path(request):
     """Run the case on the automatically chosen solve kernel (quad32 / generic wavefront where they apply),
-    on the general chain kernel, on the generic wavefront kernel, and on the one-row-per-step wave32 kernel."""
+    on the general chain kernel, on the generic wavefront kernel, on the one-row-per-step wave32 kernel and on
+    the many-vector kernel (8 vectors per warp; forced even for a single vector)."""
     from block_diag_ilu_b200 import _lib
-    old = _lib.lib().bdilu_debug_force_chain_solve({"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3}[request.param])
+    old = _lib.lib().bdilu_debug_force_chain_solve(PATHS[request.param])
     yield request.param
     _lib.lib().bdilu_debug_force_chain_solve(old)
 
@@ -117,6 +121,67 @@ def test_wavefront_shapes(oracle, solve_path, N, w, d, ld, fam):
 def test_config4_shape(oracle):
     run_case(oracle, 1, 2048, 64, 3, "D", nrhs=4)
     run_case(oracle, 1, 256, 64, 3, "P", nrhs=2, yardstick=True)
+
+
+@pytest.fixture
+def force_mrhs():
+    from block_diag_ilu_b200 import _lib
+    old = _lib.lib().bdilu_debug_force_chain_solve(PATHS["mrhs"])
+    yield
+    _lib.lib().bdilu_debug_force_chain_solve(old)
+
+
+@pytest.mark.parametrize("fam", ["D", "P"])
+@pytest.mark.parametrize("nsys,N,w,d,ld,nrhs", [
+    (1, 300, 64, 3, 64, 19),   # cfg4's block shape, ragged last group of 8 vectors
+    (2, 40, 64, 4, 72, 8), (1, 25, 48, 2, 48, 9), (2, 30, 40, 1, 42, 5), (1, 9, 64, 0, 64, 3),
+    (3, 200, 32, 2, 32, 17), (2, 50, 32, 3, 36, 40), (2, 70, 28, 2, 28, 8), (2, 33, 16, 1, 16, 33),
+    (5, 129, 8, 2, 8, 12), (2, 64, 4, 1, 4, 70), (1, 1, 32, 0, 32, 9), (1, 2, 12, 1, 12, 2),
+    (40, 24, 32, 2, 32, 40),   # 200 groups of 8 vectors: CTAs of 2 warps sharing the staged blocks, one surplus warp per system
+    (150, 6, 16, 1, 16, 32),   # 600 groups: 4 warps per CTA
+])
+def test_many_rhs_kernel(oracle, force_mrhs, nsys, N, w, d, ld, nrhs, fam):
+    """The many-vector solve kernel (bdilu_solve_mrhs.cu): full and partial block widths, ragged vector groups,
+    one to four warps per CTA."""
+    run_case(oracle, nsys, N, w, d, fam, ld=ld, nrhs=nrhs, yardstick=(fam == "P"))
+
+
+def test_many_rhs_auto_dispatch(oracle):
+    """Automatic choice: blockw 64 with 256 vectors (cfg4's regime) and a wide batch of narrow systems with 8
+    vectors each (cfg5's shape under preconditioner reuse)."""
+    from block_diag_ilu_b200 import _lib
+    L = _lib.lib()
+    n0 = L.bdilu_launch_count()
+    run_case(oracle, 1, 64, 64, 3, "D", nrhs=256)
+    run_case(oracle, 160, 12, 8, 2, "D", nrhs=8)
+    assert L.bdilu_launch_count() > n0
+
+
+def test_many_rhs_flags(oracle, force_mrhs):
+    """NaN in b and a zero U diagonal reported per vector exactly as ILU_inplace::solve does (:491-495)."""
+    N, w, d = 12, 64, 2
+    data, b = synth.make_batch(1, N, w, d, "D", seed0=11, ld=w, nrhs=10)
+    b[0, 3, 5 * w + 7] = np.nan
+    b[0, 3, 9 * w + 1] = np.nan
+    b[0, 9, 0] = np.nan
+    ilu = dev.BatchedILU(torch.from_numpy(data).cuda(), N, w, d, ld=w, copy=True)
+    ilu.solve(torch.from_numpy(b).cuda())
+    flags = ilu.flags.cpu().numpy()[0]
+    want = np.zeros(10, dtype=np.int32)
+    want[3], want[9] = 5 * w + 7 + 1, 1
+    assert np.array_equal(flags, want)
+    # singular U: zero the diagonal of U in two blocks after the factorisation
+    fac = ilu.data.clone()
+    for blk, k in [(4, 10), (7, 63)]:
+        fac[0, (blk * w + k) * w + k] = 0.0
+    ilu2 = dev.BatchedILU.__new__(dev.BatchedILU)
+    ilu2.__dict__.update(ilu.__dict__)
+    ilu2.data = fac
+    b2 = np.ascontiguousarray(b[:, :2].copy())
+    b2[0, 0] = np.nan_to_num(b2[0, 0])
+    b2[0, 1] = 1.0
+    ilu2.solve(torch.from_numpy(b2).cuda())
+    assert list(ilu2.flags.cpu().numpy()[0]) == [N * w + 7 * w + 63] * 2
 
 
 def test_config5_shape_subset(oracle):
