@@ -289,7 +289,18 @@ def run_ours(args, rank, world, local_rank):
     dom_ms = max(kf, ks)
     achieved = nsys * AB[dom] / (dom_ms * 1e-3) / 1e9
     fused_gbs = nsys * AB["fused"] / (ms_per_step * 1e-3) / 1e9
-    kname = "factor_kernel<32,true,false>" if dom == "factor" else "solve_quad32_kernel<2,2,true>"
+    # kernel-name prefixes as `ncu` prints them (tools/ncu_traffic.py keys profiles/traffic.json the same way)
+    wp = 2
+    while wp < w:
+        wp *= 2
+    if dom == "factor":
+        kname = "factor_kernel<%d," % wp if w <= 32 else "factor_wide_kernel"
+    elif w > 32 and nrhs >= 3:
+        kname = "solve_mrhs_kernel<64,"
+    elif w == 32 and args.workload == "cfg3":
+        kname = "solve_quad32_kernel<"
+    else:
+        kname = "solve_wave_kernel" if w in (4, 16) and nsys * nrhs <= 8 * 148 else "solve_chain_kernel<%d>" % wp
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(kname, nsys),

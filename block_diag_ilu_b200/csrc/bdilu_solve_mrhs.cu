@@ -31,8 +31,7 @@ using wave::mbar_expect_tx;
 using wave::mbar_init;
 using wave::mbar_wait;
 
-constexpr int Q = 4;       // lanes sharing one vector
-constexpr int R = 32 / Q;  // vectors per warp
+// Q = lanes sharing one vector (4, 8 or 16; template parameter), R = 32 / Q vectors per warp
 constexpr int NS = 4;      // stages (blocks in flight)
 constexpr int MAXD = 4;    // sub/super-diagonals handled here
 constexpr int MAXWARPS = 4;
@@ -55,13 +54,15 @@ static inline Layout make_layout(int w, int ld, int ndiag)
     return L;
 }
 
-template <int WP>
+template <int WP, int Q>
 struct Cfg {
+    static_assert(WP >= 2 * Q, "every lane owns at least one row pair");
+    static constexpr int R = 32 / Q;         // vectors per warp
     static constexpr int NP = WP / (2 * Q);  // row pairs per lane
-    static constexpr int RPL = 2 * NP;       // rows per lane
     static constexpr int WPP = WP + 8;       // pitch of one vector in the coupling ring (bank spread)
 };
 
+template <int Q>
 __device__ __forceinline__ double quad_bcast(double v, int src)
 {
     int lo = __shfl_sync(FULL, __double2loint(v), src, Q);
@@ -69,14 +70,14 @@ __device__ __forceinline__ double quad_bcast(double v, int src)
     return __hiloint2double(hi, lo);
 }
 
-template <int WP, bool FULLW>
+template <int WP, int Q, bool FULLW>
 __global__ void __launch_bounds__(MAXWARPS * 32)
 solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                   const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
                   int *__restrict__ flags, int groups_per_sys, int ctas_per_sys, Layout SL, int dbg)
 {
-    using C = Cfg<WP>;
-    constexpr int NP = C::NP, WPP = C::WPP;
+    using C = Cfg<WP, Q>;
+    constexpr int NP = C::NP, WPP = C::WPP, R = C::R;
     extern __shared__ __align__(128) unsigned char smem[];
     const int nwc = blockDim.x >> 5;
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
@@ -261,8 +262,8 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
                     const double *c1 = c0 + ld;
                     double y0 = acc[io];
                     double y1 = fma(-c0[2 * pk + 1], y0, acc[io + 1]);  // unit lower L (:503-507)
-                    y0 = quad_bcast(y0, qo);
-                    y1 = quad_bcast(y1, qo);
+                    y0 = quad_bcast<Q>(y0, qo);
+                    y1 = quad_bcast<Q>(y1, qo);
                     if (q == qo) acc[io + 1] = y1;
 #pragma unroll
                     for (int i = pk / Q; i < NP; ++i) {
@@ -291,8 +292,8 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
                     const double *c1 = c0 + ld;
                     double x1 = acc[io + 1] * dinv[2 * pk + 1];
                     double x0 = fma(-c1[2 * pk], x1, acc[io]) * dinv[2 * pk];  // U[2pk, 2pk+1] (:519-523, 531-532)
-                    x0 = quad_bcast(x0, qo);
-                    x1 = quad_bcast(x1, qo);
+                    x0 = quad_bcast<Q>(x0, qo);
+                    x1 = quad_bcast<Q>(x1, qo);
                     if (q == qo) {
                         acc[io] = x0;
                         acc[io + 1] = x1;
@@ -350,19 +351,19 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
         flags[(int64_t)sys * V.nrhs + rhs] = (nan_first != 0x7fffffff) ? nan_first : (zero_last >= 0 ? N * w + zero_last : 0);
 }
 
-template <int WP, bool FULLW>
+template <int WP, int Q, bool FULLW>
 static cudaError_t launch_t(unsigned grid, int nwc, size_t smem, const double *data, int64_t sys_stride, const Dims &D,
                             const int *rowbycol, const int *colbyrow, const double *b, double *x, const VecLayout &V,
                             int *flags, int gps, int cps, const Layout &SL, cudaStream_t st)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(solve_mrhs_kernel<WP, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(solve_mrhs_kernel<WP, Q, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     static const int dbg = getenv("BDILU_MRHS_DBG") ? atoi(getenv("BDILU_MRHS_DBG")) : 0;  // timing experiments only
-    solve_mrhs_kernel<WP, FULLW><<<grid, nwc * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps,
+    solve_mrhs_kernel<WP, Q, FULLW><<<grid, nwc * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps,
                                                                 cps, SL, dbg);
     return cudaGetLastError();
 }
@@ -383,15 +384,27 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     if ((reinterpret_cast<uintptr_t>(data) | reinterpret_cast<uintptr_t>(rowbycol) | reinterpret_cast<uintptr_t>(colbyrow)) & 15)
         return false;
     if (((int64_t)D.nblocks * w) & 3) return false;  // per-system offset of the permutation vectors stays 16-byte aligned
+    const int WP = w <= 8 ? 8 : w <= 16 ? 16 : w <= 32 ? 32 : 64;
+    const bool fullw = w == WP;
     if (g_solve_path == 0) {
-        // Measured on B200 (scratch/mrhs_time.py): blockw 64 has no wavefront kernel to compete with (17.8 ms vs 44.9 ms
-        // on cfg4, even with one group of 8 vectors).  At blockw 32 a quad32 CTA finishes one vector per SM 14x faster
-        // than a warp here finishes its 8, so this path only wins from ~14 waves of one-vector CTAs on; narrower blocks
-        // switch as soon as the wavefront kernels decline the batch (more than 8 waves).
+        // Measured on B200 (scratch/mrhs_time.py): blockw 64 has no wavefront kernel to compete with.  At blockw 32 a
+        // quad32 CTA finishes one vector per SM 14x faster than a warp here finishes its 8, so this path only wins from
+        // ~14 waves of one-vector CTAs on; narrower blocks switch as soon as the wavefront kernels decline the batch
+        // (more than 8 waves).
         const int64_t nvec = (int64_t)nsys * V.nrhs;
-        const bool use = w > 32 ? V.nrhs >= 3 : (V.nrhs >= R && nvec > (w == 32 ? 14 : 8) * 148);
+        const bool use = w > 32 ? V.nrhs >= 3 : (V.nrhs >= 8 && nvec > (w == 32 ? 14 : 8) * 148);
         if (!use) return false;
     }
+    // Lanes per vector: 4 is the most efficient split (8 vectors share every L/U load); when that leaves most of the
+    // GPU idle (cfg4: 256 vectors = 32 warps) the rows of a block are spread over 8 or 16 lanes instead, which shortens
+    // each warp's instruction stream per block (the chain over the blocks is what bounds the run time).
+    static const int q_env = getenv("BDILU_MRHS_Q") ? atoi(getenv("BDILU_MRHS_Q")) : 0;  // experiments only
+    int Q = 4;
+    if (fullw) {
+        while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 32 / Q - 1) / (32 / Q)) < 2 * 148) Q *= 2;
+        if (q_env == 4 || ((q_env == 8 || q_env == 16) && WP >= 2 * q_env)) Q = q_env;
+    }
+    const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const int64_t total_groups = (int64_t)nsys * gps;
     int nwc = (int)((total_groups + 147) / 148);
@@ -399,23 +412,33 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     if (nwc > gps) nwc = gps;
     if (nwc < 1) nwc = 1;
     const int cps = (gps + nwc - 1) / nwc;
-    const int WP = w <= 8 ? 8 : w <= 16 ? 16 : w <= 32 ? 32 : 64;
     const Layout SL = make_layout(w, D.ld, D.ndiag);
     const int Dr = D.ndiag > 0 ? D.ndiag : 1;
     const size_t smem = (size_t)NS * SL.stage_bytes + 2 * NS * 8 + (size_t)nwc * Dr * R * (WP + 8) * 8 + (size_t)nwc * WP * 8;
     if (smem > 227 * 1024) return false;
     const int64_t grid = (int64_t)nsys * cps;
     if (grid > 0x7fffffff) return false;
-    const bool fullw = w == WP;
-#define BDILU_MRHS(WPV)                                                                                                  \
-    *err = fullw ? launch_t<WPV, true>((unsigned)grid, nwc, smem, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, \
-                                       gps, cps, SL, st)                                                                 \
-                 : launch_t<WPV, false>((unsigned)grid, nwc, smem, data, sys_stride, D, rowbycol, colbyrow, b, x, V,      \
-                                        flags, gps, cps, SL, st);
-    if (WP == 8) BDILU_MRHS(8)
-    else if (WP == 16) BDILU_MRHS(16)
-    else if (WP == 32) BDILU_MRHS(32)
-    else BDILU_MRHS(64)
+#define BDILU_MRHS(WPV, QV, FW)                                                                                      \
+    *err = launch_t<WPV, QV, FW>((unsigned)grid, nwc, smem, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps, \
+                                 cps, SL, st)
+    if (!fullw) {
+        if (WP == 8) BDILU_MRHS(8, 4, false);
+        else if (WP == 16) BDILU_MRHS(16, 4, false);
+        else if (WP == 32) BDILU_MRHS(32, 4, false);
+        else BDILU_MRHS(64, 4, false);
+    } else if (Q == 4) {
+        if (WP == 8) BDILU_MRHS(8, 4, true);
+        else if (WP == 16) BDILU_MRHS(16, 4, true);
+        else if (WP == 32) BDILU_MRHS(32, 4, true);
+        else BDILU_MRHS(64, 4, true);
+    } else if (Q == 8) {
+        if (WP == 16) BDILU_MRHS(16, 8, true);
+        else if (WP == 32) BDILU_MRHS(32, 8, true);
+        else BDILU_MRHS(64, 8, true);
+    } else {
+        if (WP == 32) BDILU_MRHS(32, 16, true);
+        else BDILU_MRHS(64, 16, true);
+    }
 #undef BDILU_MRHS
     count_launch(1);
     return true;
