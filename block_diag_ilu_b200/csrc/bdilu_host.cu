@@ -196,7 +196,8 @@ struct Workspace {
     std::mutex mu;
     double *d_data = nullptr, *d_b = nullptr, *d_x = nullptr;
     int *d_idx = nullptr, *d_info = nullptr, *d_flags = nullptr;
-    size_t cap_data = 0, cap_vec = 0, cap_x = 0, cap_idx = 0, cap_info = 0, cap_flags = 0;
+    int *h_codes = nullptr;  // pinned staging for info + flags (see bdilu_host_factor_solve)
+    size_t cap_data = 0, cap_vec = 0, cap_x = 0, cap_idx = 0, cap_info = 0, cap_flags = 0, cap_codes = 0;
     cudaStream_t st[3] = {nullptr, nullptr, nullptr};
 };
 Workspace g_ws;
@@ -234,6 +235,17 @@ extern "C" int bdilu_host_factor_solve(const double *host_data, int64_t sys_stri
     CUH(grow(W.d_idx, W.cap_idx, (size_t)3 * nsys * n));
     CUH(grow(W.d_info, W.cap_info, (size_t)nsys));
     CUH(grow(W.d_flags, W.cap_flags, (size_t)nsys * nrhs));
+    // info/flags land in a pinned staging buffer and are handed over after the last slab: an asynchronous copy into
+    // the caller's (usually pageable) int arrays would block the host at every slab and serialise the pipeline
+    // (measured: 124 ms instead of ~93 ms per cfg3 batch).
+    const size_t ncodes = (size_t)nsys + (size_t)nsys * nrhs;
+    if (ncodes > W.cap_codes) {
+        if (W.h_codes) cudaFreeHost(W.h_codes);
+        W.h_codes = nullptr; W.cap_codes = 0;
+        CUH(cudaHostAlloc((void **)&W.h_codes, ncodes * sizeof(int), cudaHostAllocDefault));
+        W.cap_codes = ncodes;
+    }
+    int *h_info = W.h_codes, *h_flags = W.h_codes + nsys;
     int *d_ipiv = W.d_idx, *d_rbc = W.d_idx + (size_t)nsys * n, *d_cbr = W.d_idx + (size_t)2 * nsys * n;
 
     // slabs of systems round-robin over 3 streams: H2D(slab k+1) overlaps factor+solve(slab k) and D2H(slab k-1)
@@ -259,11 +271,13 @@ extern "C" int bdilu_host_factor_solve(const double *host_data, int64_t sys_stri
         if (rc) return rc;
         CUH(cudaMemcpyAsync(host_x + (size_t)s0 * nrhs * n, W.d_x + (size_t)s0 * nrhs * n,
                             sizeof(double) * (size_t)ns * nrhs * n, cudaMemcpyDeviceToHost, st));
-        if (info) CUH(cudaMemcpyAsync(info + s0, W.d_info + s0, sizeof(int) * ns, cudaMemcpyDeviceToHost, st));
+        if (info) CUH(cudaMemcpyAsync(h_info + s0, W.d_info + s0, sizeof(int) * ns, cudaMemcpyDeviceToHost, st));
         if (flags)
-            CUH(cudaMemcpyAsync(flags + (size_t)s0 * nrhs, W.d_flags + (size_t)s0 * nrhs, sizeof(int) * (size_t)ns * nrhs,
+            CUH(cudaMemcpyAsync(h_flags + (size_t)s0 * nrhs, W.d_flags + (size_t)s0 * nrhs, sizeof(int) * (size_t)ns * nrhs,
                                 cudaMemcpyDeviceToHost, st));
     }
     for (auto &s : W.st) CUH(cudaStreamSynchronize(s));
+    if (info) memcpy(info, h_info, sizeof(int) * (size_t)nsys);
+    if (flags) memcpy(flags, h_flags, sizeof(int) * (size_t)nsys * nrhs);
     return BDILU_OK;
 }
