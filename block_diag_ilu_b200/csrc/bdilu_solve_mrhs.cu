@@ -4,20 +4,25 @@
 // Krylov vector; the reference has no multi-RHS entry point).
 //
 // The one-vector kernels spend a whole SM (quad32) or a whole warp plus a private pass over the factors (chain
-// kernel) per vector.  Here a warp carries R = 8 vectors at once:
-//   lane = (j, q): j = vector inside the warp's group of R, q = which quarter of the block's row PAIRS the lane owns
-//   (pair p = i*Q + q holds rows 2p, 2p+1; Q = 4).  A block of the factor is staged ONCE per CTA by one bulk copy
+// kernel) per vector.  Here a warp carries R = 32/Q vectors at once (Q = 4, 8 or 16 lanes per vector):
+//   lane = (j, q): j = vector inside the warp's group of R, q = which share of the block's row PAIRS the lane owns
+//   (pair p = i*Q + q holds rows 2p, 2p+1).  A block of the factor is staged ONCE per CTA by one bulk copy
 //   (cp.async.bulk + mbarrier, NS-deep ring) together with its permutation vectors and the sub/sup rows it needs,
 //   and is consumed from shared memory by every warp of the CTA: the L/U entries of a row pair come from one
-//   LDS.128 whose address depends on q only (4 distinct addresses per warp, a broadcast for the R vectors).
+//   LDS.128 whose address depends on q only (Q distinct addresses per warp, a broadcast for the R vectors).
 //   The triangular solve advances TWO columns per step: the owner of pair p finishes both values locally, two
-//   width-4 shuffles hand them to the other three lanes of the vector, every lane updates its later (forward) or
+//   width-Q shuffles hand them to the other lanes of the vector, every lane updates its later (forward) or
 //   earlier (backward) pairs with 4 DFMA per pair.  The last ndiag blocks' results live in a per-warp shared ring
 //   for the coupling terms; b (forward) and y (backward) are prefetched one block ahead into registers.
 //   Backward: 1/U[k,k] is computed once per block per warp (lanes split the diagonal), the zero-diagonal flag of
 //   :533-534 is taken there; x = acc * (1/u) differs from the reference's acc / u by at most one rounding.
 // Blocks are read once per CTA and sweep (not once per vector): cfg4 moves 2 x 67 MB x (CTAs) through L2 instead
 // of 256 x that.
+// Measured on B200 (scratch/mrhs_time.py, profiles/r01_ncu_full_summary.md): cfg4 solve 44.9 ms (chain kernel) ->
+// 18.9 ms (Q=4, 32 warps) -> 14.2 ms (Q=16, 128 warps).  What bounds it is the dependent sequence of one vector's
+// chain -- 2 sweeps x 2048 blocks x 32 two-column steps of shuffle + 3 DFMA (~130 cycles each) plus ~2000 cycles per
+// block of staging/coupling/publication -- not bandwidth (60 GB/s of DRAM traffic) and not the FP64 pipe (4 %):
+// the next step is the wavefront over consecutive blocks that the blockw-32 one-vector kernel already has.
 #include <stdlib.h>
 
 #include "bdilu_wave_common.cuh"
@@ -74,7 +79,7 @@ template <int WP, int Q, bool FULLW>
 __global__ void __launch_bounds__(MAXWARPS * 32)
 solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                   const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
-                  int *__restrict__ flags, int groups_per_sys, int ctas_per_sys, Layout SL, int dbg)
+                  int *__restrict__ flags, int groups_per_sys, int ctas_per_sys, Layout SL)
 {
     using C = Cfg<WP, Q>;
     constexpr int NP = C::NP, WPP = C::WPP, R = C::R;
@@ -165,9 +170,9 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
         const bool fwd = it < N;
         const int bi = fwd ? it : NIT - 1 - it;
         const int s = it % NS;
-        if (producer && it + NS - 1 < NIT && !(dbg & 16 && it >= NS)) issue(it + NS - 1);
+        if (producer && it + NS - 1 < NIT) issue(it + NS - 1);
         __syncwarp();
-        if (!(dbg & 16 && it >= NS)) mbar_wait(&full[s], (it / NS) & 1);
+        mbar_wait(&full[s], (it / NS) & 1);
         const unsigned char *stg = stages + (size_t)s * SL.stage_bytes;
         const double *blk = reinterpret_cast<const double *>(stg);
         const int *cbr_s = reinterpret_cast<const int *>(stg + SL.o_cbr);
@@ -190,7 +195,7 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
         }
         {
             const int dmax = fwd ? min(nd, bi) : min(nd, N - 1 - bi);
-            if (dmax > 0 && !(dbg & 8)) {
+            if (dmax > 0) {
                 int ci[2 * NP];
 #pragma unroll
                 for (int i = 0; i < NP; ++i) {
@@ -223,11 +228,11 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
         }
 
         // ---- prefetch the next block's right-hand side (b through rowbycol, or y written by this thread) ----
-        if (it + 1 < NIT && it + 1 != N && !(dbg & 2)) {
+        if (it + 1 < NIT && it + 1 != N) {
             const int nit = it + 1;
             if (nit < N) {
                 const int ns = nit % NS;
-                if (!(dbg & 16 && nit >= NS)) mbar_wait(&full[ns], (nit / NS) & 1);
+                mbar_wait(&full[ns], (nit / NS) & 1);
                 const int *rbc_n = reinterpret_cast<const int *>(stages + (size_t)ns * SL.stage_bytes + SL.o_rbc);
                 const double *bn = bq + (int64_t)nit * w;
 #pragma unroll
@@ -252,8 +257,7 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
         }
 
         // ---- triangular solve of the block, two columns per step ----
-        if (dbg & 1) {
-        } else if (fwd) {
+        if (fwd) {
 #pragma unroll
             for (int pk = 0; pk < WP / 2; ++pk) {
                 if (FULLW || pk < hw) {
@@ -326,7 +330,7 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
                 const int p = i * Q + q;
                 if (FULLW || p < hw) {
                     *reinterpret_cast<double2 *>(rg + 2 * p) = make_double2(acc[2 * i], acc[2 * i + 1]);
-                    if (live && !(dbg & 4)) {
+                    if (live) {
                         xo[2 * p] = acc[2 * i];
                         xo[2 * p + 1] = acc[2 * i + 1];
                     }
@@ -334,7 +338,7 @@ solve_mrhs_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, c
             }
         }
         __syncwarp();
-        if (lane == 0 && !(dbg & 16)) mbar_arrive(&empty[s]);
+        if (lane == 0) mbar_arrive(&empty[s]);
         if (fwd) {
             if (it + 1 < N) slot = slot + 1 == Dr ? 0 : slot + 1;
         } else {
@@ -362,9 +366,8 @@ static cudaError_t launch_t(unsigned grid, int nwc, size_t smem, const double *d
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    static const int dbg = getenv("BDILU_MRHS_DBG") ? atoi(getenv("BDILU_MRHS_DBG")) : 0;  // timing experiments only
     solve_mrhs_kernel<WP, Q, FULLW><<<grid, nwc * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps,
-                                                                cps, SL, dbg);
+                                                                cps, SL);
     return cudaGetLastError();
 }
 
