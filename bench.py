@@ -296,7 +296,7 @@ def run_ours(args, rank, world, local_rank):
     if dom == "factor":
         kname = "factor_kernel<%d," % wp if w <= 32 else "factor_wide_kernel"
     elif w > 32 and nrhs >= 3:
-        kname = "solve_mrhs_kernel<64,"
+        kname = "solve_mrhs_wave_kernel<64,"
     elif w == 32 and args.workload == "cfg3":
         kname = "solve_quad32_kernel<"
     else:

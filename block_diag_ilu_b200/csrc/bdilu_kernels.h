@@ -24,7 +24,8 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const VecLayout &V, int *flags, cudaStream_t st);
 
 extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
-                          // 4 = many-vector kernel whenever the shape allows it, 5 = automatic without the many-vector kernel
+                          // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
+                          // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
 bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
@@ -40,6 +41,10 @@ cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double
 bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
                              const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                              cudaStream_t st, cudaError_t *err);
+
+bool try_launch_solve_mrhs_wave(int Q, const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
+                                const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
+                                cudaStream_t st, cudaError_t *err);
 
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st);

@@ -25,55 +25,10 @@
 // the next step is the wavefront over consecutive blocks that the blockw-32 one-vector kernel already has.
 #include <stdlib.h>
 
-#include "bdilu_wave_common.cuh"
+#include "bdilu_mrhs_common.cuh"
 
 namespace bdilu {
 namespace mrhs {
-
-using wave::bulk_g2s;
-using wave::mbar_arrive;
-using wave::mbar_expect_tx;
-using wave::mbar_init;
-using wave::mbar_wait;
-
-// Q = lanes sharing one vector (4, 8 or 16; template parameter), R = 32 / Q vectors per warp
-constexpr int NS = 4;      // stages (blocks in flight)
-constexpr int MAXD = 4;    // sub/super-diagonals handled here
-constexpr int MAXWARPS = 4;
-
-struct Layout {
-    int blk_bytes, idx_bytes, diag_bytes;  // bulk-copy sizes
-    int o_rbc, o_cbr, o_diag, stage_bytes;
-};
-
-static inline Layout make_layout(int w, int ld, int ndiag)
-{
-    Layout L;
-    L.blk_bytes = w * ld * 8;
-    L.idx_bytes = w * 4;
-    L.diag_bytes = w * 8;
-    L.o_rbc = L.blk_bytes;
-    L.o_cbr = L.o_rbc + L.idx_bytes;
-    L.o_diag = L.o_cbr + L.idx_bytes;
-    L.stage_bytes = (L.o_diag + ndiag * L.diag_bytes + 127) & ~127;
-    return L;
-}
-
-template <int WP, int Q>
-struct Cfg {
-    static_assert(WP >= 2 * Q, "every lane owns at least one row pair");
-    static constexpr int R = 32 / Q;         // vectors per warp
-    static constexpr int NP = WP / (2 * Q);  // row pairs per lane
-    static constexpr int WPP = WP + 8;       // pitch of one vector in the coupling ring (bank spread)
-};
-
-template <int Q>
-__device__ __forceinline__ double quad_bcast(double v, int src)
-{
-    int lo = __shfl_sync(FULL, __double2loint(v), src, Q);
-    int hi = __shfl_sync(FULL, __double2hiint(v), src, Q);
-    return __hiloint2double(hi, lo);
-}
 
 template <int WP, int Q, bool FULLW>
 __global__ void __launch_bounds__(MAXWARPS * 32)
@@ -381,7 +336,7 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     using namespace mrhs;
     *err = cudaSuccess;
     const int w = D.w;
-    if (g_solve_path != 0 && g_solve_path != 4) return false;
+    if (g_solve_path != 0 && g_solve_path != 4 && g_solve_path != 6) return false;
     if (w > 64 || w < 4 || (w & 3) || (D.ld & 1) || D.ndiag > MAXD || D.nsat != 0 || D.nblocks < 1) return false;
     if (sys_stride & 1) return false;
     if ((reinterpret_cast<uintptr_t>(data) | reinterpret_cast<uintptr_t>(rowbycol) | reinterpret_cast<uintptr_t>(colbyrow)) & 15)
@@ -389,24 +344,43 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     if (((int64_t)D.nblocks * w) & 3) return false;  // per-system offset of the permutation vectors stays 16-byte aligned
     const int WP = w <= 8 ? 8 : w <= 16 ? 16 : w <= 32 ? 32 : 64;
     const bool fullw = w == WP;
-    if (g_solve_path == 0) {
-        // Measured on B200 (scratch/mrhs_time.py): blockw 64 has no wavefront kernel to compete with.  At blockw 32 a
-        // quad32 CTA finishes one vector per SM 14x faster than a warp here finishes its 8, so this path only wins from
-        // ~14 waves of one-vector CTAs on; narrower blocks switch as soon as the wavefront kernels decline the batch
-        // (more than 8 waves).
-        const int64_t nvec = (int64_t)nsys * V.nrhs;
-        const bool use = w > 32 ? V.nrhs >= 3 : (V.nrhs >= 8 && nvec > (w == 32 ? 14 : 8) * 148);
-        if (!use) return false;
-    }
     // Lanes per vector: 4 is the most efficient split (8 vectors share every L/U load); when that leaves most of the
-    // GPU idle (cfg4: 256 vectors = 32 warps) the rows of a block are spread over 8 or 16 lanes instead, which shortens
+    // GPU idle (cfg4: 256 vectors = 32 groups) the rows of a block are spread over 8 or 16 lanes instead, which shortens
     // each warp's instruction stream per block (the chain over the blocks is what bounds the run time).
     static const int q_env = getenv("BDILU_MRHS_Q") ? atoi(getenv("BDILU_MRHS_Q")) : 0;  // experiments only
     int Q = 4;
     if (fullw) {
-        while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 32 / Q - 1) / (32 / Q)) < 2 * 148) Q *= 2;
+        while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 16 / Q - 1) / (16 / Q)) <= 2 * 148) Q *= 2;
         if (q_env == 4 || ((q_env == 8 || q_env == 16) && WP >= 2 * q_env)) Q = q_env;
     }
+    const int64_t nvec = (int64_t)nsys * V.nrhs;
+    const int64_t groups = (int64_t)nsys * ((V.nrhs + 32 / Q - 1) / (32 / Q));
+    // The wavefront form (bdilu_solve_mrhs_wave.cu: one CTA per group, K warps on consecutive blocks) shortens the
+    // chain's latency; it pays while the GPU is not full of groups.  With more groups than that the one-warp-per-group
+    // form below has the better throughput (blocks staged once for up to 4 groups).
+    bool wave = fullw && groups <= 2 * 148;
+    if (g_solve_path == 0) {
+        // Measured on B200 (scratch/mrhs_time.py).  blockw 64 has no one-vector wavefront kernel to compete with
+        // (cfg4: chain 44.9 ms, one warp per group 13.5 ms, wavefront form 7.7 ms).  At blockw 32 a quad32 CTA finishes
+        // one vector per SM in 2.6 ms (N = 8192) where a wavefront group takes 16-29 ms and a one-warp group 34 ms:
+        // 1024 vectors take 19.0 ms one by one against 29.3 ms in wavefront groups, so only the one-warp form is used
+        // there, from ~14 waves of one-vector CTAs on (2048 vectors: 36 ms against 37.8 ms).  Narrower blocks:
+        // the wavefront form matches the generic one-vector kernel at one wave (blockw 16, 64 vectors: 1.19 vs 1.30 ms)
+        // and the one-warp form takes over once the one-vector kernels decline the batch (more than 8 waves).
+        bool use;
+        if (w > 32) use = V.nrhs >= 3;
+        else if (V.nrhs < 8) use = false;
+        else if (w == 32) {
+            wave = false;
+            use = nvec > 14 * 148;
+        }
+        else use = wave ? nvec >= 64 : nvec > 8 * 148;
+        if (!use) return false;
+    }
+    if (g_solve_path == 4) wave = false;
+    if (g_solve_path == 6) wave = fullw;
+    if (wave && try_launch_solve_mrhs_wave(Q, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, err))
+        return true;
     const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const int64_t total_groups = (int64_t)nsys * gps;

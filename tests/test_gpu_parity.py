@@ -91,7 +91,7 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4}
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6}
 
 
 @pytest.fixture(params=list(PATHS))
@@ -123,11 +123,13 @@ def test_config4_shape(oracle):
     run_case(oracle, 1, 256, 64, 3, "P", nrhs=2, yardstick=True)
 
 
-@pytest.fixture
-def force_mrhs():
+@pytest.fixture(params=["mrhs", "mrhs_wave"])
+def force_mrhs(request):
+    """Both many-vector kernels: one warp per group of vectors, and the wavefront form (K warps of a CTA on
+    consecutive blocks; full power-of-two widths, other widths fall back to the first)."""
     from block_diag_ilu_b200 import _lib
-    old = _lib.lib().bdilu_debug_force_chain_solve(PATHS["mrhs"])
-    yield
+    old = _lib.lib().bdilu_debug_force_chain_solve(PATHS[request.param])
+    yield request.param
     _lib.lib().bdilu_debug_force_chain_solve(old)
 
 
@@ -139,6 +141,7 @@ def force_mrhs():
     (5, 129, 8, 2, 8, 12), (2, 64, 4, 1, 4, 70), (1, 1, 32, 0, 32, 9), (1, 2, 12, 1, 12, 2),
     (40, 24, 32, 2, 32, 40),   # 200 groups of 8 vectors: CTAs of 2 warps sharing the staged blocks, one surplus warp per system
     (150, 6, 16, 1, 16, 32),   # 600 groups: 4 warps per CTA
+    (1, 2048, 64, 3, 64, 16), (2, 1000, 32, 2, 32, 8), (3, 700, 16, 4, 16, 9), (4, 900, 8, 1, 8, 8),  # long chains
 ])
 def test_many_rhs_kernel(oracle, force_mrhs, nsys, N, w, d, ld, nrhs, fam):
     """The many-vector solve kernel (bdilu_solve_mrhs.cu): full and partial block widths, ragged vector groups,
