@@ -12,7 +12,9 @@
 //   * the owner lanes of a pivot pair publish its two finished values into a ring slot [it % NSLOT][vector][row]
 //     and then bump that slot's per-vector progress word (iteration << 8 | pairs published): same thread, same
 //     shared-memory pipe, so the data is visible before the count;
-//   * the coupling terms are merged for G (1, 2 or 4) consecutive pivot pairs at a time, one group ahead of the pivot:
+//   * the coupling terms are merged for G (1, 2 or 4) consecutive pivot pairs at a time, right after the last step of
+//     the group before (blocks then trail each other by ~G+1 steps; merging a whole group earlier hides the merge
+//     latency but doubles the distance, measured slower: cfg4 7.7 vs 6.6 ms):
 //     every lane polls the progress words of its vector until the predecessors have published the furthest pair the
 //     permutation of the group's rows points at; inside a group every pair has its own owner lane, so the G pairs
 //     are merged by one branch-free instruction sequence (volatile reads of the ring);
@@ -37,6 +39,11 @@ constexpr int KMAX = 6;  // consumer warps per CTA
 #endif
 #ifndef BDILU_MRW_G16
 #define BDILU_MRW_G16 2
+#endif
+// 0: group g+1 is merged when group g starts (its latency hides behind G steps, blocks trail by ~2G steps);
+// 1: merged after the last step of group g (blocks trail by ~G+1 steps, the merge sits on the chain)
+#ifndef BDILU_MRW_LATE
+#define BDILU_MRW_LATE 1
 #endif
 
 struct WArgs {
@@ -210,7 +217,7 @@ __device__ __forceinline__ void block_iter(const WArgs &A, int it, double (&acc)
         merge_group(0);
 #pragma unroll
         for (int pk = 0; pk < HW; ++pk) {
-            if (pk % G == 0 && pk / G + 1 < NG) merge_group(pk / G + 1);
+            if (!BDILU_MRW_LATE && pk % G == 0 && pk / G + 1 < NG) merge_group(pk / G + 1);
             const int qo = pk % Q, io = (pk / Q) * 2;
             const double *c0 = blk + (2 * pk) * ld;
             const double *c1 = c0 + ld;
@@ -237,13 +244,14 @@ __device__ __forceinline__ void block_iter(const WArgs &A, int it, double (&acc)
                     }
                 }
             }
+            if (BDILU_MRW_LATE && pk % G == G - 1 && pk / G + 1 < NG) merge_group(pk / G + 1);
         }
     } else {
         merge_group(0);
 #pragma unroll
         for (int pkr = 0; pkr < HW; ++pkr) {
             const int pk = HW - 1 - pkr;
-            if (pkr % G == 0 && pkr / G + 1 < NG) merge_group(pkr / G + 1);
+            if (!BDILU_MRW_LATE && pkr % G == 0 && pkr / G + 1 < NG) merge_group(pkr / G + 1);
             const int qo = pk % Q, io = (pk / Q) * 2;
             const double *c0 = blk + (2 * pk) * ld;
             const double *c1 = c0 + ld;
@@ -271,6 +279,7 @@ __device__ __forceinline__ void block_iter(const WArgs &A, int it, double (&acc)
                     }
                 }
             }
+            if (BDILU_MRW_LATE && pkr % G == G - 1 && pkr / G + 1 < NG) merge_group(pkr / G + 1);
         }
     }
 
