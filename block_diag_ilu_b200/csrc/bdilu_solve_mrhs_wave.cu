@@ -32,7 +32,7 @@ namespace mrhs {
 using wave::ld_volatile_s;
 using wave::st_volatile_s;
 
-constexpr int KMAX = 6;  // consumer warps per CTA
+constexpr int KMAX = 8;  // consumer warps per CTA
 // pivot pairs per coupling merge at blockw 64 / blockw 32 (narrower blocks merge pair by pair)
 #ifndef BDILU_MRW_G32
 #define BDILU_MRW_G32 4
@@ -300,8 +300,10 @@ __device__ __forceinline__ void block_iter(const WArgs &A, int it, double (&acc)
     }
 }
 
+// Register budget: ptxas' choice under a 288-thread bound measured faster at blockw 64 (6.6 -> 5.9 ms on cfg4) and slower
+// below (blockw 32: 14.5 -> 18.3 ms, blockw 16: 1.05 -> 1.72 ms) than under a 224-thread bound, so the bound follows the width.
 template <int WP, int Q>
-__global__ void __launch_bounds__((KMAX + 1) * 32)
+__global__ void __launch_bounds__(WP == 64 ? (KMAX + 1) * 32 : (KMAX - 1) * 32)
 solve_mrhs_wave_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                        const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
                        int *__restrict__ flags, int groups_per_sys, Layout SL, int NSTG)
@@ -460,7 +462,8 @@ bool try_launch_solve_mrhs_wave(int Q, const double *data, int64_t sys_stride, i
     const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const Layout SL = make_layout(w, D.ld, D.ndiag);
-    int K = k_env >= 1 && k_env <= KMAX ? k_env : KMAX;  // 6 measured best at blockw <= 32; blockw 64 fits 4
+    // measured (8 x 64 vectors at blockw 32 / 64 vectors at blockw 16): K=4 18.4 / 1.52 ms, K=6 14.4 / 1.05-1.19 ms; blockw 64 fits 4
+    int K = k_env >= 1 && k_env <= (w == 64 ? KMAX : KMAX - 2) ? k_env : (w == 64 ? 4 : 6);
     int NSTG = 0;
     size_t smem = 0;
     for (; K >= 1; --K) {
