@@ -1,7 +1,7 @@
 // Kernel 3: BlockDiagMatrix<double>::dot_vec (block_diag_ilu.hpp:295-326), the residual b - A x and
 // its squared 2-norm per (system, vector), plus scale_diag_add (:276-287).
 //
-// Purely streaming: every matrix element is read once.  One thread per output row; consecutive
+// Purely streaming: every matrix element is read once per group of up to 8 vectors.  One thread per output row; consecutive
 // threads read consecutive rows of a column-major block column, so each column load is one
 // contiguous 8*blockw-byte segment.  The reference scatters sub/sup/top/bot contributions into
 // `out`; here each row gathers the (at most 2*ndiag + satellite) couplings that land on it, so no
@@ -13,59 +13,96 @@ namespace bdilu {
 
 constexpr int MV_THREADS = 128;
 
-__device__ __forceinline__ double row_dot(const double *__restrict__ sd, const Dims &D,
-                                          const double *__restrict__ vec, int bi, int row)
+// One output row against NR vectors at once: every matrix element is loaded once per NR vectors (the vectors of one
+// system share the matrix, so a batch of right-hand sides re-reads it nrhs/NR times instead of nrhs times).
+template <int NR>
+__device__ __forceinline__ void row_dot(double (&acc)[NR], const double *__restrict__ sd, const Dims &D,
+                                        const double *const (&vec)[NR], int bi, int row)
 {
     const int w = D.w, N = D.nblocks;
     const double *col = sd + D.block(bi) + row;
-    const double *v = vec + bi * w;
-    double acc = 0.0;
-#pragma unroll 8
-    for (int c = 0; c < w; ++c) acc = fma(ld_stream(col + (int64_t)c * D.ld), __ldg(v + c), acc);
+#pragma unroll
+    for (int r = 0; r < NR; ++r) acc[r] = 0.0;
+#pragma unroll 4
+    for (int c = 0; c < w; ++c) {
+        const double a = ld_stream(col + (int64_t)c * D.ld);
+#pragma unroll
+        for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + bi * w + c), acc[r]);
+    }
     for (int di = 0; di < D.ndiag; ++di) {
-        if (bi + di + 1 < N)  // sup(di,bi,row) sits at (bi*w+row, (bi+di+1)*w+row)
-            acc = fma(ld_stream(sd + D.off_sup + D.diag_chunk(di, bi) + row), __ldg(vec + (bi + di + 1) * w + row), acc);
-        if (bi - di - 1 >= 0)  // sub(di,bi-di-1,row) sits at (bi*w+row, (bi-di-1)*w+row)
-            acc = fma(ld_stream(sd + D.off_sub + D.diag_chunk(di, bi - di - 1) + row), __ldg(vec + (bi - di - 1) * w + row), acc);
+        if (bi + di + 1 < N) {  // sup(di,bi,row) sits at (bi*w+row, (bi+di+1)*w+row)
+            const double a = ld_stream(sd + D.off_sup + D.diag_chunk(di, bi) + row);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + (bi + di + 1) * w + row), acc[r]);
+        }
+        if (bi - di - 1 >= 0) {  // sub(di,bi-di-1,row) sits at (bi*w+row, (bi-di-1)*w+row)
+            const double a = ld_stream(sd + D.off_sub + D.diag_chunk(di, bi - di - 1) + row);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + (bi - di - 1) * w + row), acc[r]);
+        }
     }
     for (int sati = 0; sati < D.nsat; ++sati) {
-        if (bi <= sati)  // top(sati,bi,row) sits at (bi*w+row, (N-1-sati+bi)*w+row)
-            acc = fma(ld_stream(sd + D.off_top + D.sat_chunk(sati, bi) + row), __ldg(vec + (N - 1 - sati + bi) * w + row), acc);
+        if (bi <= sati) {  // top(sati,bi,row) sits at (bi*w+row, (N-1-sati+bi)*w+row)
+            const double a = ld_stream(sd + D.off_top + D.sat_chunk(sati, bi) + row);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + (N - 1 - sati + bi) * w + row), acc[r]);
+        }
         const int bj = bi - N + 1 + sati;  // bot(sati,bj,row) sits at ((N-1-sati+bj)*w+row, bj*w+row)
-        if (bj >= 0)
-            acc = fma(ld_stream(sd + D.off_bot + D.sat_chunk(sati, bj) + row), __ldg(vec + bj * w + row), acc);
+        if (bj >= 0) {
+            const double a = ld_stream(sd + D.off_bot + D.sat_chunk(sati, bj) + row);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + bj * w + row), acc[r]);
+        }
     }
-    return acc;
 }
 
-// MODE 0: out = A*vec.  MODE 1: norm2 += sum (b - A*x)^2 (vec = x, rhsb = b).
-template <int MODE>
+// MODE 0: out = A*vec.  MODE 1: norm2 += sum (b - A*x)^2 (vec = x, rhsb = b).  blockIdx.y = group of NR vectors.
+template <int MODE, int NR>
 __global__ void __launch_bounds__(MV_THREADS)
 matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const double *__restrict__ vec,
               const double *__restrict__ rhsb, double *__restrict__ out, VecLayout V)
 {
-    const int sys = blockIdx.z, rhs = blockIdx.y;
+    const int sys = blockIdx.z, rhs0 = blockIdx.y * NR;
     const int n = D.nblocks * D.w;
     const int i = blockIdx.x * MV_THREADS + threadIdx.x;
     const double *sd = data + (int64_t)sys * sys_stride;
-    const int64_t voff = (int64_t)sys * V.sys_stride + (int64_t)rhs * V.rhs_stride;
-    double val = 0.0;
+    int64_t voff[NR];
+    const double *vp[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const int rhs = rhs0 + r < V.nrhs ? rhs0 + r : V.nrhs - 1;  // a ragged last group repeats its last vector
+        voff[r] = (int64_t)sys * V.sys_stride + (int64_t)rhs * V.rhs_stride;
+        vp[r] = vec + voff[r];
+    }
+    double val[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) val[r] = 0.0;
     if (i < n) {
         const int bi = i / D.w, row = i - bi * D.w;
-        val = row_dot(sd, D, vec + voff, bi, row);
-        if (MODE == 0) out[voff + i] = val;
-        else { val = __ldg(rhsb + voff + i) - val; val *= val; }
+        row_dot<NR>(val, sd, D, vp, bi, row);
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            if (MODE == 0) {
+                if (rhs0 + r < V.nrhs) out[voff[r] + i] = val[r];
+            } else {
+                val[r] = __ldg(rhsb + voff[r] + i) - val[r];
+                val[r] *= val[r];
+            }
+        }
     }
     if (MODE == 1) {
-        __shared__ double part[MV_THREADS / 32];
+        __shared__ double part[NR][MV_THREADS / 32];
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) val += group_bcast<32>(val, (threadIdx.x & 31) ^ off);
-        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = val;
+        for (int r = 0; r < NR; ++r) {
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) val[r] += group_bcast<32>(val[r], (threadIdx.x & 31) ^ off);
+            if ((threadIdx.x & 31) == 0) part[r][threadIdx.x >> 5] = val[r];
+        }
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x < NR && rhs0 + threadIdx.x < V.nrhs) {
             double s = 0.0;
-            for (int k = 0; k < MV_THREADS / 32; ++k) s += part[k];
-            atomicAdd(out + (int64_t)sys * V.nrhs + rhs, s);
+            for (int k = 0; k < MV_THREADS / 32; ++k) s += part[threadIdx.x][k];
+            atomicAdd(out + (int64_t)sys * V.nrhs + rhs0 + threadIdx.x, s);
         }
     }
 }
@@ -97,8 +134,11 @@ cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, con
     const int n = D.nblocks * D.w;
     if (n == 0 || nsys == 0 || V.nrhs == 0) return cudaSuccess;
     if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
-    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, V.nrhs, nsys);
-    matvec_kernel<0><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
+    const int nr = V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1);
+    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
+    if (nr == 8) matvec_kernel<0, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
+    else if (nr == 4) matvec_kernel<0, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
+    else matvec_kernel<0, 1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
     count_launch(1);
     return cudaGetLastError();
 }
@@ -112,8 +152,11 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
     if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
     if (e != cudaSuccess || n == 0) return e;
-    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, V.nrhs, nsys);
-    matvec_kernel<1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
+    const int nr = V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1);
+    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
+    if (nr == 8) matvec_kernel<1, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
+    else if (nr == 4) matvec_kernel<1, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
+    else matvec_kernel<1, 1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
     count_launch(1);
     return cudaGetLastError();
 }

@@ -198,13 +198,14 @@ def test_satellites(oracle, nsat):
     run_case(oracle, 2, 6, 8, 0, "P", nsat=nsat, ld=8)
 
 
-def test_dot_vec_and_residual(oracle):
+@pytest.mark.parametrize("nrhs", [3, 5, 11])   # one vector per pass, ragged groups of 4 and of 8 vectors per pass
+def test_dot_vec_and_residual(oracle, nrhs):
     for (N, w, d, ld, nsat) in [(3, 4, 2, 4, 0), (50, 32, 2, 32, 0), (20, 16, 1, 19, 0), (9, 64, 3, 64, 0), (7, 4, 1, 4, 2)]:
-        data, b = synth.make_batch(2, N, w, d, "P", seed0=3, ld=ld, nrhs=3, nsat=nsat)
+        data, b = synth.make_batch(2, N, w, d, "P", seed0=3, ld=ld, nrhs=nrhs, nsat=nsat)
         dd, vv = torch.from_numpy(data).cuda(), torch.from_numpy(b).cuda()
         out = dev.dot_vec(dd, vv, N, w, d, nsat=nsat, ld=ld).cpu().numpy()
         for s in range(2):
-            for r in range(3):
+            for r in range(nrhs):
                 want = oracle.dot_vec(data[s].copy(), N, w, d, nsat, ld, b[s, r])
                 assert np.abs(out[s, r] - want).max() <= 1e-13 * max(1.0, np.abs(want).max())
         # residual of x = 0 is ||b||^2; residual of A x' with b = A x' is ~0
