@@ -81,6 +81,37 @@ def ncu_traffic(kernel, nsys):
         return None
 
 
+def bind_host_to_gpu_numa(index):
+    """Run this rank's host thread (and so its pinned allocations) on the NUMA node the GPU hangs off.
+
+    The e2e leg of every rank streams ~5 GB per step from pinned host memory; with 8 ranks on one host the copies of
+    a rank whose buffers sit on the far socket cross the inter-socket link.  Returns the node, or None when the
+    topology cannot be read (then nothing is changed)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        dev = "%s:%s" % (dom[-4:], rest)
+        with open("/sys/bus/pci/devices/%s/numa_node" % dev.lower()) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons through NVML while the timed regions run."""
 
@@ -322,6 +353,7 @@ def run_ours(args, rank, world, local_rank):
 
     # e2e through the host-pointer C ABI on every rank's slab: pinned host buffers, H2D + fused + D2H inside the timed
     # region; barrier on both sides, max over ranks (each GPU has its own PCIe link, the host memory is shared)
+    numa_node = bind_host_to_gpu_numa(local_rank) if world > 1 else None
     h_data = torch.empty(pristine.shape, dtype=torch.float64, pin_memory=True)
     h_b = torch.empty(b.shape, dtype=torch.float64, pin_memory=True)
     h_x = torch.empty(b.shape, dtype=torch.float64, pin_memory=True)
@@ -353,6 +385,7 @@ def run_ours(args, rank, world, local_rank):
                    "h2d_bytes_per_step": int(world * (h_data.numel() * 8 + h_b.numel() * 8)),
                    "d2h_bytes_per_step": int(world * (h_x.numel() * 8 + 4 * nsys + 4 * nsys * nrhs)), "ms_per_step": 1e3 * t_e2e,
                    "steps": e2e_steps, "n_gpus": world, "bit_identical_to_device_path": e2e_diff == 0.0,
+                   "host_numa_node_rank0": numa_node,
                    "api": "bdilu_host_factor_solve (host-pointer C ABI; pinned host buffers; slabs of systems pipelined "
                           "over 3 streams; one call per rank on its own slab of the batch, max over ranks)"}
     sampler.stop_flag = True
