@@ -326,7 +326,7 @@ def run_ours(args, rank, world, local_rank):
         wp *= 2
     if dom == "factor":
         kname = "factor_kernel<%d," % wp if w <= 32 else "factor_wide_kernel"
-    elif w > 32 and nrhs >= 3:
+    elif w > 32:
         kname = "solve_mrhs_wave_kernel<64,"
     elif w == 32 and args.workload == "cfg3":
         kname = "solve_quad32_kernel<"

@@ -368,7 +368,7 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
         // the wavefront form matches the generic one-vector kernel at one wave (blockw 16, 64 vectors: 1.19 vs 1.30 ms)
         // and the one-warp form takes over once the one-vector kernels decline the batch (more than 8 waves).
         bool use;
-        if (w > 32) use = V.nrhs >= 3;
+        if (w > 32) use = true;  // even one vector: 5.9 ms in a wavefront group against ~40 ms on the chain kernel
         else if (V.nrhs < 8) use = false;
         else if (w == 32) {
             wave = false;

@@ -88,6 +88,8 @@ BDILU_API int bdilu_factor(double *data, int64_t sys_stride, int nsys,
  *   0 ok; 1..n = 1-based index of the first NaN in b; n + k = zero U diagonal at 0-based row k
  *   (first error wins in the reference's loop order, :500-501, 533-534).  x is always written.
  * b and x must not alias (they are __restrict__ in the reference).
+ * The nrhs vectors of a system share its factor: batches of them (any number at blockw > 32, >= 8 otherwise, size permitting)
+ * run on kernels that read every block once per group of 2-8 vectors instead of once per vector.
  * y_scratch: nullable; unused by the current kernels (y stays on chip), kept for ABI stability. */
 BDILU_API int bdilu_solve(const double *data, int64_t sys_stride, int nsys,
                 int nblocks, int blockw, int ndiag, int nsat, int ld,
