@@ -369,12 +369,17 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
         // and the one-warp form takes over once the one-vector kernels decline the batch (more than 8 waves).
         bool use;
         if (w > 32) use = true;  // even one vector: 5.9 ms in a wavefront group against ~40 ms on the chain kernel
-        else if (V.nrhs < 8) use = false;
         else if (w == 32) {
             wave = false;
-            use = nvec > 14 * 148;
+            use = V.nrhs >= 8 && nvec > 14 * 148;
+        } else if (wave) {
+            // blockw 8 / 16 while the GPU is not full of groups: the wavefront group kernel also beats the one-vector
+            // kernels on a single vector (blockw 16, N = 1024, 1 system: 1.05 vs 1.29 ms; blockw 8, N = 512, 64 systems:
+            // 0.53 vs 0.71 ms) once the chain is long enough to amortise its pipeline fill
+            use = D.nblocks >= 128;
+        } else {
+            use = V.nrhs >= 8 && nvec > 8 * 148;
         }
-        else use = wave ? nvec >= 64 : nvec > 8 * 148;
         if (!use) return false;
     }
     if (g_solve_path == 4) wave = false;
