@@ -372,11 +372,15 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
         else if (w == 32) {
             wave = false;
             use = V.nrhs >= 8 && nvec > 14 * 148;
-        } else if (wave) {
-            // blockw 8 / 16 while the GPU is not full of groups: the wavefront group kernel also beats the one-vector
-            // kernels on a single vector (blockw 16, N = 1024, 1 system: 1.05 vs 1.29 ms; blockw 8, N = 512, 64 systems:
-            // 0.53 vs 0.71 ms) once the chain is long enough to amortise its pipeline fill
-            use = D.nblocks >= 128;
+        } else if (D.nblocks >= 128 && fullw) {
+            // blockw 8 / 16, chains long enough to amortise the pipeline fill.  The group kernels also beat the
+            // one-vector kernels when every group holds a single live vector (ms, one vector per system):
+            //   blockw 16, N = 1024:   1 system  1.05 wavefront / 1.29 one-vector;  296: 1.26 / 2.58;
+            //                          600: 3.60 wavefront, 3.27 one warp per group / 6.32;  1200: 6.18, 3.65 / 6.83
+            //   blockw 8, N = 512:     64: 0.53 / 0.71;  512: 0.74 / 2.38;  1024: 1.37, 1.49 / 2.45;
+            //                          1536: 2.03, 1.58 / 2.41;  2048: 2.58, 1.77 / 2.39;  4096: 4.87, 3.30 / 2.41
+            wave = groups <= (w == 8 ? 1024 : 2 * 148);
+            use = wave || groups <= (w == 8 ? 2560 : 2400) || (V.nrhs >= 8 && nvec > 8 * 148);
         } else {
             use = V.nrhs >= 8 && nvec > 8 * 148;
         }
