@@ -313,3 +313,25 @@ def test_factor_scaled_in_place_and_refactor():
     inpl = Jd.clone()
     c = dev.BatchedILU.from_scaled(inpl, -0.2, 1.0, N, w, d, out=inpl)
     assert torch.equal(c.data, want.data)
+
+
+def test_many_rhs_wavefront_repeatable():
+    """The wavefront group kernel publishes row pairs between warps through shared memory; a race there would show up
+    as a rare difference between repeats of the same solve.  Repeats must be bit-identical and agree with the chain
+    kernel (scratch/mrhs_stress.py is the long form of this test)."""
+    from block_diag_ilu_b200 import _lib
+    L = _lib.lib()
+    for (nsys, N, w, d, nrhs, fam) in [(2, 600, 64, 3, 20, "P"), (6, 1500, 16, 2, 5, "D"), (50, 400, 8, 2, 1, "P")]:
+        data, b = synth.make_batch_device(nsys, N, w, d, torch.device("cuda:0"), seed=11, nrhs=nrhs, family=fam)
+        ilu = dev.BatchedILU(data, N, w, d, check=False)
+        old = L.bdilu_debug_force_chain_solve(PATHS["chain"])
+        try:
+            ref = ilu.solve(b).clone()
+            L.bdilu_debug_force_chain_solve(PATHS["mrhs_wave"])
+            first = ilu.solve(b).clone()
+            for _ in range(10):
+                assert torch.equal(ilu.solve(b), first)
+        finally:
+            L.bdilu_debug_force_chain_solve(old)
+        rel = float(((first - ref).abs().amax(dim=-1) / ref.abs().amax(dim=-1)).max())
+        assert rel < 1e-12
