@@ -15,19 +15,30 @@ constexpr int MV_THREADS = 128;
 
 // One output row against NR vectors at once: every matrix element is loaded once per NR vectors (the vectors of one
 // system share the matrix, so a batch of right-hand sides re-reads it nrhs/NR times instead of nrhs times).
+// `vs`: this block's slice of the NR vectors staged in shared memory as [column][NR] (NR > 1), else nullptr.
 template <int NR>
 __device__ __forceinline__ void row_dot(double (&acc)[NR], const double *__restrict__ sd, const Dims &D,
-                                        const double *const (&vec)[NR], int bi, int row)
+                                        const double *const (&vec)[NR], const double *vs, int bi, int row)
 {
     const int w = D.w, N = D.nblocks;
     const double *col = sd + D.block(bi) + row;
 #pragma unroll
     for (int r = 0; r < NR; ++r) acc[r] = 0.0;
+    if (NR > 1) {
 #pragma unroll 4
-    for (int c = 0; c < w; ++c) {
-        const double a = ld_stream(col + (int64_t)c * D.ld);
+        for (int c = 0; c < w; ++c) {
+            const double a = ld_stream(col + (int64_t)c * D.ld);
+            const double2 *v2 = reinterpret_cast<const double2 *>(vs + c * NR);  // one broadcast LDS.128 per two vectors
 #pragma unroll
-        for (int r = 0; r < NR; ++r) acc[r] = fma(a, __ldg(vec[r] + bi * w + c), acc[r]);
+            for (int r = 0; r < NR / 2; ++r) {
+                const double2 v = v2[r];
+                acc[2 * r] = fma(a, v.x, acc[2 * r]);
+                acc[2 * r + 1] = fma(a, v.y, acc[2 * r + 1]);
+            }
+        }
+    } else {
+#pragma unroll 8
+        for (int c = 0; c < w; ++c) acc[0] = fma(ld_stream(col + (int64_t)c * D.ld), __ldg(vec[0] + bi * w + c), acc[0]);
     }
     for (int di = 0; di < D.ndiag; ++di) {
         if (bi + di + 1 < N) {  // sup(di,bi,row) sits at (bi*w+row, (bi+di+1)*w+row)
@@ -77,9 +88,24 @@ matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const
     double val[NR];
 #pragma unroll
     for (int r = 0; r < NR; ++r) val[r] = 0.0;
+    // NR > 1: the slice of the vectors under this CTA's blocks goes to shared memory once, transposed to [column][NR]
+    constexpr int MAXW = 64;
+    __shared__ __align__(16) double vs[NR > 1 ? (MV_THREADS + 2 * MAXW) * NR : 1];
+    const int i0 = blockIdx.x * MV_THREADS;
+    const int b_lo = i0 / D.w;
+    if (NR > 1) {
+        const int last = min(n - 1, i0 + MV_THREADS - 1);
+        const int len = (last / D.w + 1 - b_lo) * D.w;  // whole blocks: < MV_THREADS + 2 w
+        for (int idx = threadIdx.x; idx < len * NR; idx += MV_THREADS) {
+            const int r = idx / len, c = idx - r * len;
+            const int rhs = rhs0 + r < V.nrhs ? rhs0 + r : V.nrhs - 1;
+            vs[c * NR + r] = __ldg(vec + (int64_t)sys * V.sys_stride + (int64_t)rhs * V.rhs_stride + b_lo * D.w + c);
+        }
+        __syncthreads();
+    }
     if (i < n) {
         const int bi = i / D.w, row = i - bi * D.w;
-        row_dot<NR>(val, sd, D, vp, bi, row);
+        row_dot<NR>(val, sd, D, vp, vs + (bi - b_lo) * D.w * NR, bi, row);
 #pragma unroll
         for (int r = 0; r < NR; ++r) {
             if (MODE == 0) {
@@ -134,7 +160,7 @@ cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, con
     const int n = D.nblocks * D.w;
     if (n == 0 || nsys == 0 || V.nrhs == 0) return cudaSuccess;
     if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
-    const int nr = V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1);
+    const int nr = D.w > 64 ? 1 : (V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1));  // the staged slice is sized for blockw <= 64
     dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
     if (nr == 8) matvec_kernel<0, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
     else if (nr == 4) matvec_kernel<0, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
@@ -152,7 +178,7 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
     if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
     if (e != cudaSuccess || n == 0) return e;
-    const int nr = V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1);
+    const int nr = D.w > 64 ? 1 : (V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1));  // the staged slice is sized for blockw <= 64
     dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
     if (nr == 8) matvec_kernel<1, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
     else if (nr == 4) matvec_kernel<1, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
