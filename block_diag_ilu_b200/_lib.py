@@ -33,12 +33,18 @@ _SIGNATURES = {
     "bdilu_host_dot_vec": (_i, [_p] + _DIMS + [_p, _p, _i]),
     "bdilu_host_scale_diag_add": (_i, [_p, _p] + _DIMS + [_d, _d]),
     "bdilu_host_factor_solve": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _p, _p]),
-    "bdilu_debug_force_chain_solve": (_i, [_i]),
     "bdilu_launch_count": (_i64, []),
     "bdilu_launch_count_reset": (None, []),
 }
 
+# include/bdilu_internal.h: test and measurement hooks, not part of the drop-in boundary
+_INTERNAL = {
+    "bdilu_debug_force_chain_solve": (_i, [_i]),
+    "bdilu_debug_skew_stats": (_i, [_p, _i]),
+}
+
 EXPORTED = tuple(_SIGNATURES)
+EXPORTED_INTERNAL = tuple(_INTERNAL)
 _lib = None
 
 
@@ -54,7 +60,7 @@ def lib():
     if _lib is None:
         path = os.environ.get("BDILU_LIB_PATH") or _build.build()  # override: instrumented debug builds
         L = C.CDLL(path)
-        for name, (res, args) in _SIGNATURES.items():
+        for name, (res, args) in list(_SIGNATURES.items()) + list(_INTERNAL.items()):
             fn = getattr(L, name)  # AttributeError here == ABI drift: fail loudly
             fn.restype = res
             fn.argtypes = args

@@ -7,6 +7,7 @@
 #include <string>
 
 #include "../../include/bdilu.h"
+#include "../../include/bdilu_internal.h"
 #include "bdilu_kernels.h"
 
 namespace bdilu {
@@ -103,6 +104,16 @@ int bdilu_debug_force_chain_solve(int on)
     const int old = g_solve_path;
     g_solve_path = on;
     return old;
+}
+
+int bdilu_debug_skew_stats(int64_t *out3, int reset)
+{
+    unsigned long long v[3] = {0, 0, 0};
+    cudaError_t e = skew_stats(v, reset != 0);
+    if (e != cudaSuccess) return fail(BDILU_ERR_CUDA, cudaGetErrorString(e));
+    if (out3)
+        for (int i = 0; i < 3; ++i) out3[i] = (int64_t)v[i];
+    return BDILU_OK;
 }
 
 int64_t bdilu_launch_count(void) { return g_launches.load(); }

@@ -23,7 +23,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
-extern int g_solve_path;  // test hook: 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
+extern int g_solve_path;  // test hook (7 = blockw 32: general wavefront kernel without the systolic first pass): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
                           // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
                           // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
@@ -38,13 +38,25 @@ cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double
                                 const int *rowbycol, const int *colbyrow, const double *b, double *x,
                                 const VecLayout &V, int *flags, cudaStream_t st);
 
+// status (nullable): int per vector; when given, only the vectors with status != 0 are solved (second pass behind
+// the systolic kernel)
 bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
                              const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
-                             cudaStream_t st, cudaError_t *err);
+                             cudaStream_t st, cudaError_t *err, const int *status = nullptr);
+
+// blockw == 32 systolic solve (bdilu_solve_skew.cu): one warp per vector, lane = block, consecutive blocks one row
+// apart.  Handles the vectors whose permutations are the identity (status == 0 after the permutation scan) and hands
+// the others back through status.  Returns false when the shape does not fit.
+bool try_launch_solve_skew32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
+                             const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
+                             int *status, cudaStream_t st, cudaError_t *err);
 
 bool try_launch_solve_mrhs_wave(int Q, const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                                 const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                                 cudaStream_t st, cudaError_t *err);
+
+// counters of the systolic solve (test hook): solved / handed back at the end / skipped at the start
+cudaError_t skew_stats(unsigned long long out[3], bool reset);
 
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st);

@@ -315,12 +315,9 @@ static cudaError_t launch_t(unsigned grid, int nwc, size_t smem, const double *d
                             const int *rowbycol, const int *colbyrow, const double *b, double *x, const VecLayout &V,
                             int *flags, int gps, int cps, const Layout &SL, cudaStream_t st)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(solve_mrhs_kernel<WP, Q, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    // the attribute belongs to the (function, device) pair: set on every launch (cheap), not once per process
+    cudaError_t e = cudaFuncSetAttribute(solve_mrhs_kernel<WP, Q, FULLW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
     solve_mrhs_kernel<WP, Q, FULLW><<<grid, nwc * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps,
                                                                 cps, SL);
     return cudaGetLastError();
@@ -347,11 +344,9 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     // Lanes per vector: 4 is the most efficient split (8 vectors share every L/U load); when that leaves most of the
     // GPU idle (cfg4: 256 vectors = 32 groups) the rows of a block are spread over 8 or 16 lanes instead, which shortens
     // each warp's instruction stream per block (the chain over the blocks is what bounds the run time).
-    static const int q_env = getenv("BDILU_MRHS_Q") ? atoi(getenv("BDILU_MRHS_Q")) : 0;  // experiments only
     int Q = 4;
     if (fullw) {
         while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 16 / Q - 1) / (16 / Q)) <= 2 * 148) Q *= 2;
-        if (q_env == 4 || ((q_env == 8 || q_env == 16) && WP >= 2 * q_env)) Q = q_env;
     }
     const int64_t nvec = (int64_t)nsys * V.nrhs;
     const int64_t groups = (int64_t)nsys * ((V.nrhs + 32 / Q - 1) / (32 / Q));

@@ -436,12 +436,9 @@ static cudaError_t launch_w(unsigned grid, int K, size_t smem, const double *dat
                             const int *rowbycol, const int *colbyrow, const double *b, double *x, const VecLayout &V,
                             int *flags, int gps, const Layout &SL, int NSTG, cudaStream_t st)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(solve_mrhs_wave_kernel<WP, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    // per (function, device): set on every launch
+    cudaError_t e = cudaFuncSetAttribute(solve_mrhs_wave_kernel<WP, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
     solve_mrhs_wave_kernel<WP, Q><<<grid, (K + 1) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, gps,
                                                                      SL, NSTG);
     return cudaGetLastError();
@@ -458,12 +455,11 @@ bool try_launch_solve_mrhs_wave(int Q, const double *data, int64_t sys_stride, i
     *err = cudaSuccess;
     const int w = D.w;
     if (!(w == 8 || w == 16 || w == 32 || w == 64) || w < 2 * Q) return false;
-    static const int k_env = getenv("BDILU_MRW_K") ? atoi(getenv("BDILU_MRW_K")) : 0;  // experiments only
     const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const Layout SL = make_layout(w, D.ld, D.ndiag);
     // measured (8 x 64 vectors at blockw 32 / 64 vectors at blockw 16): K=4 18.4 / 1.52 ms, K=6 14.4 / 1.05-1.19 ms; blockw 64 fits 4
-    int K = k_env >= 1 && k_env <= (w == 64 ? KMAX : KMAX - 2) ? k_env : (w == 64 ? 4 : 6);
+    int K = (w == 64 ? 4 : 6);
     int NSTG = 0;
     size_t smem = 0;
     for (; K >= 1; --K) {

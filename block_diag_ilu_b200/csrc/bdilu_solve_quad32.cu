@@ -408,11 +408,13 @@ template <int ND, int MODE, bool LD32>
 __global__ void __launch_bounds__((QW + NP) * 32, 1)
 solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const int *__restrict__ rowbycol,
                     const int *__restrict__ colbyrow, const double *__restrict__ bvec, double *xvec, VecLayout V,
-                    int *__restrict__ flags, int NS, int dbg)
+                    int *__restrict__ flags, int NS, int dbg, const int *__restrict__ status)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int vecid = blockIdx.x;
+    // second pass behind the systolic kernel (bdilu_solve_skew.cu): only the vectors it handed back (status != 0)
+    if (status != nullptr && status[vecid] == 0) return;
     const int sys = vecid / V.nrhs, rhs = vecid % V.nrhs;
     const int N = D.nblocks;
 
@@ -482,36 +484,39 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     }
 }
 
-// BDILU_QUAD_DBG (read once): timing experiments only (every variant gives correct results).
-//   2 = one producer warp, 4 = one bulk copy per block instead of per group,
-//   32 / 64 / 128 (builds with -DBDILU_QUAD_VARIANTS only) = chain variant: shuffle quads (32), lean chain merging
-//   the coupling every 4 rows (64) or every row (128); default: lean chain, every 2 rows (the fastest on B200)
+// Timing experiments (builds with -DBDILU_QUAD_VARIANTS=<mask> only; every variant gives correct results):
+//   2 = one producer warp, 4 = one bulk copy per block instead of per group, 32 / 64 / 128 = chain variant: shuffle
+//   quads (32), lean chain merging the coupling every 4 rows (64) or every row (128).  Product builds: lean chain,
+//   coupling merged every 2 rows (the fastest on B200); nothing is read from the environment.
 static int debug_switches()
 {
-    static const int v = getenv("BDILU_QUAD_DBG") ? atoi(getenv("BDILU_QUAD_DBG")) : 0;
-    return v;
+#ifdef BDILU_QUAD_VARIANTS
+    return BDILU_QUAD_VARIANTS;
+#else
+    return 0;
+#endif
 }
 
 template <int ND, int MODE, bool LD32>
 static cudaError_t launch_one(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
                               const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
-                              const VecLayout &V, int *flags)
+                              const VecLayout &V, int *flags, const int *status)
 {
     cudaError_t e = cudaFuncSetAttribute(solve_quad32_kernel<ND, MODE, LD32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          227 * 1024);
     if (e != cudaSuccess) return e;
     solve_quad32_kernel<ND, MODE, LD32><<<nvec, (QW + NP) * 32, smem, st>>>(data, sys_stride, D, rowbycol, colbyrow, b, x,
-                                                                            V, flags, NS, debug_switches());
+                                                                            V, flags, NS, debug_switches(), status);
     return cudaGetLastError();
 }
 
 template <int ND>
 static cudaError_t launch_nd(unsigned nvec, size_t smem, int NS, cudaStream_t st, const double *data, int64_t sys_stride,
                              const Dims &D, const int *rowbycol, const int *colbyrow, const double *b, double *x,
-                             const VecLayout &V, int *flags)
+                             const VecLayout &V, int *flags, const int *status)
 {
-#define Q32_ARGS nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags
-#ifdef BDILU_QUAD_VARIANTS  // the other chain variants, for timing comparisons (BDILU_QUAD_DBG = 32 / 64 / 128)
+#define Q32_ARGS nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status
+#ifdef BDILU_QUAD_VARIANTS  // the other chain variants, for timing comparisons
     const int dbg = debug_switches();
     if (dbg & 32) return launch_one<ND, 0, false>(Q32_ARGS);
     if (dbg & 64) return launch_one<ND, 4, false>(Q32_ARGS);
@@ -540,7 +545,7 @@ extern "C" __attribute__((visibility("default"))) int bdilu_debug_q32prof(unsign
 // Returns false when the shape does not fit (too few stages): the caller falls back to the older kernels.
 bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
                              const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
-                             cudaStream_t st, cudaError_t *err)
+                             cudaStream_t st, cudaError_t *err, const int *status)
 {
     using namespace quad;
     const GroupLayout GL = group_layout(D.ld, D.ndiag);
@@ -551,10 +556,10 @@ bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stri
     if (NS * G < QW + 2 * G) return false;  // the stages must cover every consumer warp plus groups in flight
     const size_t smem = (size_t)NS * (GL.bytes + 16) + fixed;
     switch (D.ndiag) {
-    case 1: *err = launch_nd<1>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags); break;
-    case 2: *err = launch_nd<2>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags); break;
-    case 3: *err = launch_nd<3>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags); break;
-    default: *err = launch_nd<4>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags); break;
+    case 1: *err = launch_nd<1>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status); break;
+    case 2: *err = launch_nd<2>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status); break;
+    case 3: *err = launch_nd<3>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status); break;
+    default: *err = launch_nd<4>(nvec, smem, NS, st, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status); break;
     }
     return true;
 }

@@ -249,13 +249,33 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
     if (NS > MAX_STAGES) NS = MAX_STAGES;
     if (NS < NW + 2) return false;
     const size_t smem = (size_t)NS * (SL.bytes + 16) + fixed;
-    static bool attr_set = false;
-    if (!attr_set) {
-        *err = cudaFuncSetAttribute(solve_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget);
-        if (*err != cudaSuccess) return true;
-        attr_set = true;
+    // per (function, device): set on every launch
+    *err = cudaFuncSetAttribute(solve_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget);
+    if (*err != cudaSuccess) return true;
+    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5)) {
+        // Systolic kernel first (vectors of systems that never pivoted), the general wavefront kernel behind it for
+        // the vectors handed back through `status` (stream-ordered scratch: one int per vector).
+        int *status = nullptr;
+        if (cudaMallocAsync(reinterpret_cast<void **>(&status), sizeof(int) * (size_t)nvec, st) == cudaSuccess) {
+            if (try_launch_solve_skew32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status, st, err)) {
+                if (*err == cudaSuccess &&
+                    try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err, status)) {
+                    count_launch(1);
+                    cudaFreeAsync(status, st);
+                    return true;
+                }
+                // the general kernel does not fit this shape either way: fall through with the scratch released; the
+                // paths below redo every vector
+                cudaFreeAsync(status, st);
+                if (*err != cudaSuccess) return true;
+            } else {
+                cudaFreeAsync(status, st);
+            }
+        } else {
+            (void)cudaGetLastError();
+        }
     }
-    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5) &&
+    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5 || g_solve_path == 7) &&
         try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err)) {
         count_launch(1);
         return true;

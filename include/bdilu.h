@@ -20,8 +20,9 @@
  *   b + s*sys_rhs_stride + r*rhs_stride   (each vector contiguous, nblocks*blockw doubles).
  *
  * Device entry points (bdilu_factor ... bdilu_residual_norm2) take DEVICE pointers and a
- * cudaStream_t passed as void*; they are asynchronous, reentrant, allocate nothing and never
- * synchronise.  Host entry points (bdilu_ilu_*, bdilu_host_*) take HOST pointers, own the device
+ * cudaStream_t passed as void*; they are asynchronous, reentrant and never synchronise; the only
+ * allocation is stream-ordered scratch of one int per vector inside bdilu_solve at blockw 32 (cudaMallocAsync /
+ * cudaFreeAsync on the caller's stream).  Host entry points (bdilu_ilu_*, bdilu_host_*) take HOST pointers, own the device
  * mirrors, and block until the result is in host memory (the reference's calls are blocking).
  *
  * Return value of every int function: 0 = ok, <0 = BDILU_ERR_* (see bdilu_last_error()).
@@ -174,11 +175,6 @@ BDILU_API int bdilu_host_scale_diag_add(double *host_dst, const double *host_src
 BDILU_API int bdilu_host_factor_solve(const double *host_data, int64_t sys_stride, int nsys,
                             int nblocks, int blockw, int ndiag, int nsat, int ld,
                             const double *host_b, double *host_x, int nrhs, int *info, int *flags);
-
-/* Test hook: 1 forces bdilu_solve onto the general chain kernel, 2 onto the generic wavefront kernel,
- * even where a faster kernel applies (every path is parity-tested); 0 = automatic.  Returns the
- * previous setting. */
-BDILU_API int bdilu_debug_force_chain_solve(int on);
 
 /* Kernels launched by this library since load / last reset (bench.py's gpu_launches claim). */
 BDILU_API int64_t bdilu_launch_count(void);

@@ -1,0 +1,31 @@
+/*
+ * bdilu_internal.h -- test and measurement hooks of libbdilu_b200.so.  NOT part of the drop-in boundary
+ * (include/bdilu.h): nothing here corresponds to a reference interface, callers of the reference never see it.
+ * The hooks are process-global and not thread-safe; tests/ and bench.py are their only users.
+ */
+#ifndef BDILU_INTERNAL_H
+#define BDILU_INTERNAL_H
+
+#include <stdint.h>
+
+#include "bdilu.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Solve-kernel selection: 0 = automatic; 1 = general chain kernel; 2 = generic wavefront kernel; 3 = one-row wave32
+ * kernel; 4 / 6 = many-vector kernels (one warp per group / wavefront form) whenever the shape allows; 5 = automatic
+ * without the many-vector kernels; 7 = blockw 32: general wavefront kernel (quad32) without the systolic first pass.
+ * Every path is parity-tested.  Returns the previous setting. */
+BDILU_API int bdilu_debug_force_chain_solve(int on);
+
+/* Vectors handled by the systolic blockw-32 solve since load / last reset: out[0] = solved by it, out[1] = handed
+ * to the general kernel at the end (NaN in b, U diagonal outside the fast reciprocal's range), out[2] = skipped at
+ * the start (the system pivoted).  Synchronises the device. */
+BDILU_API int bdilu_debug_skew_stats(int64_t *out3, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BDILU_INTERNAL_H */

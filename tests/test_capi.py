@@ -15,14 +15,20 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "bdilu.h")
 
 
-def declared_symbols():
-    src = open(HEADER).read()
+INTERNAL_HEADER = os.path.join(ROOT, "include", "bdilu_internal.h")
+
+
+def declared_symbols(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"BDILU_API\s+[^;(]*?\b(bdilu_\w+)\s*\(", src)))
 
 
 def test_header_declares_what_the_binding_binds():
     assert set(declared_symbols()) == set(_lib.EXPORTED)
+    # test hooks live in their own header, outside the drop-in boundary
+    assert set(declared_symbols(INTERNAL_HEADER)) == set(_lib.EXPORTED_INTERNAL)
+    assert not any("debug" in s for s in declared_symbols())
 
 
 def test_library_exports_every_declared_symbol():
@@ -33,7 +39,8 @@ def test_library_exports_every_declared_symbol():
     exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
     assert set(declared_symbols()) <= exported
     # nothing but the C ABI leaks out (kernels and helpers are hidden)
-    assert all(s.startswith("bdilu_") for s in exported), sorted(exported - set(declared_symbols()))[:5]
+    assert exported == set(declared_symbols()) | set(declared_symbols(INTERNAL_HEADER)), \
+        sorted(exported ^ (set(declared_symbols()) | set(declared_symbols(INTERNAL_HEADER))))[:5]
 
 
 def test_header_compiles_as_plain_c(tmp_path):
