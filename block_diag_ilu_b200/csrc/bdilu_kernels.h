@@ -23,7 +23,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
                          const int *rowbycol, const int *colbyrow, const double *b, double *x,
                          const VecLayout &V, int *flags, cudaStream_t st);
 
-extern int g_solve_path;  // test hook (7 = blockw 32: general wavefront kernel without the systolic first pass): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
+extern int g_solve_path;  // test hook (7 = quad32; 8 = experimental systolic blockw-32 kernel first, quad32 behind it): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
                           // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
                           // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
@@ -44,7 +44,7 @@ bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stri
                              const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                              cudaStream_t st, cudaError_t *err, const int *status = nullptr);
 
-// blockw == 32 systolic solve (bdilu_solve_skew.cu): one warp per vector, lane = block, consecutive blocks one row
+// blockw == 32 systolic solve (bdilu_solve_skew.cu; experimental, opt-in): lane = block, consecutive blocks one row
 // apart.  Handles the vectors whose permutations are the identity (status == 0 after the permutation scan) and hands
 // the others back through status.  Returns false when the shape does not fit.
 bool try_launch_solve_skew32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,

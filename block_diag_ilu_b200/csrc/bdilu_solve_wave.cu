@@ -252,9 +252,10 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
     // per (function, device): set on every launch
     *err = cudaFuncSetAttribute(solve_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget);
     if (*err != cudaSuccess) return true;
-    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5)) {
-        // Systolic kernel first (vectors of systems that never pivoted), the general wavefront kernel behind it for
-        // the vectors handed back through `status` (stream-ordered scratch: one int per vector).
+    if (w == 32 && g_solve_path == 8) {
+        // EXPERIMENTAL, opt-in (test hook 8; measured slower than quad32 on B200, see bdilu_solve_skew.cu): systolic
+        // kernel first (vectors of systems that never pivoted), the general wavefront kernel behind it for the vectors
+        // handed back through `status` (stream-ordered scratch: one int per vector).
         int *status = nullptr;
         if (cudaMallocAsync(reinterpret_cast<void **>(&status), sizeof(int) * (size_t)nvec, st) == cudaSuccess) {
             if (try_launch_solve_skew32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, status, st, err)) {
@@ -275,7 +276,7 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
             (void)cudaGetLastError();
         }
     }
-    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5 || g_solve_path == 7) &&
+    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5 || g_solve_path == 7 || g_solve_path == 8) &&
         try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err)) {
         count_launch(1);
         return true;

@@ -16,11 +16,12 @@ extern "C" {
 
 /* Solve-kernel selection: 0 = automatic; 1 = general chain kernel; 2 = generic wavefront kernel; 3 = one-row wave32
  * kernel; 4 / 6 = many-vector kernels (one warp per group / wavefront form) whenever the shape allows; 5 = automatic
- * without the many-vector kernels; 7 = blockw 32: general wavefront kernel (quad32) without the systolic first pass.
+ * without the many-vector kernels; 7 = same as 0 at blockw 32 (quad32); 8 = blockw 32: experimental systolic kernel first, quad32 behind it for the
+ * vectors it hands back (csrc/bdilu_solve_skew.cu; slower than quad32 on B200, kept for the record).
  * Every path is parity-tested.  Returns the previous setting. */
 BDILU_API int bdilu_debug_force_chain_solve(int on);
 
-/* Vectors handled by the systolic blockw-32 solve since load / last reset: out[0] = solved by it, out[1] = handed
+/* Vectors seen by the experimental systolic blockw-32 solve (hook 8) since load / last reset: out[0] = solved by it, out[1] = handed
  * to the general kernel at the end (NaN in b, U diagonal outside the fast reciprocal's range), out[2] = skipped at
  * the start (the system pivoted).  Synchronises the device. */
 BDILU_API int bdilu_debug_skew_stats(int64_t *out3, int reset);
