@@ -153,13 +153,61 @@ def factor_solve(data, b, nblocks, blockw, ndiag, nsat=0, ld=None):
     return x3.view(shp), ilu
 
 
-def dot_vec(data, vec, nblocks, blockw, ndiag, nsat=0, ld=None):
+class GraphedFactorSolve:
+    """`ILU<double> ilu(A); ilu.solve(b, x)` for small batches, captured once in a CUDA graph.
+
+    A batch that fits one wave (BASELINE configs 1, 2, and one-GPU slabs of config 5) is bound by launch latency: the
+    copy of A into the work buffer (the owning-ILU deep copy, block_diag_ilu.hpp:546-547), the factor launch, its
+    info memset and the solve launch are recorded once and replayed with a single cudaGraphLaunch.  `a` and `b` are
+    the STATIC input tensors (update them in place between replays); results land in `x`, `info`, `flags`.
+    """
+
+    def __init__(self, a, b, nblocks, blockw, ndiag, nsat=0, ld=None):
+        _lib.require_device()
+        self.shape = Shape(nblocks, blockw, ndiag, nsat, ld)
+        self.a = _check_data(a, self.shape)
+        self.nsys = self.a.shape[0]
+        dev, n = self.a.device, self.shape.n
+        self.b, self._shp = _vec3(b, self.nsys, n)
+        nrhs = self.b.shape[1]
+        self.work = torch.empty_like(self.a)
+        self.ipiv = torch.empty((self.nsys, n), dtype=torch.int32, device=dev)
+        self.rowbycol = torch.empty_like(self.ipiv)
+        self.colbyrow = torch.empty_like(self.ipiv)
+        self.info = torch.empty((self.nsys,), dtype=torch.int32, device=dev)
+        self.flags = torch.empty((self.nsys, nrhs), dtype=torch.int32, device=dev)
+        self._x3 = torch.empty_like(self.b)
+        self.x = self._x3.view(self._shp)
+
+        def body():
+            self.work.copy_(self.a)
+            _lib.check(_lib.lib().bdilu_factor_solve(
+                _lib.ptr(self.work), self.work.stride(0), self.nsys, *self.shape.dims(),
+                _lib.ptr(self.ipiv), _lib.ptr(self.rowbycol), _lib.ptr(self.colbyrow), _lib.ptr(self.info),
+                _lib.ptr(self.b), _lib.ptr(self._x3), nrhs, n, n * nrhs, _lib.ptr(self.flags), _stream()))
+
+        with torch.cuda.device(dev):
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                body()  # warm-up outside the capture (function attributes, lazy module load)
+            torch.cuda.current_stream().wait_stream(side)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                body()
+
+    def replay(self):
+        self.graph.replay()
+        return self.x
+
+
+def dot_vec(data, vec, nblocks, blockw, ndiag, nsat=0, ld=None, out=None):
     """A @ vec for the UNFACTORED packed batch (BlockDiagMatrix::dot_vec, block_diag_ilu.hpp:295-326)."""
     _lib.require_device()
     shape = Shape(nblocks, blockw, ndiag, nsat, ld)
     data = _check_data(data, shape)
     v3, shp = _vec3(vec, data.shape[0], shape.n)
-    out = torch.empty_like(v3)
+    out = torch.empty_like(v3) if out is None else _vec3(out, data.shape[0], shape.n)[0]
     with torch.cuda.device(data.device):
         _lib.check(_lib.lib().bdilu_dot_vec(
             _lib.ptr(data), data.stride(0), data.shape[0], *shape.dims(), _lib.ptr(v3), _lib.ptr(out),

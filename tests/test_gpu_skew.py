@@ -118,5 +118,5 @@ def test_full_shape_two_systems_and_repeatability(oracle):
 def test_wide_batch_of_vectors(oracle):
     """More vectors than SMs: 40 systems x 8 vectors = 320 CTAs in three waves."""
     stats(reset=True)
-    run_case(oracle, 40, 24, 32, 2, "D", nrhs=8, seed0=3)
+    run_case(oracle, 40, 80, 32, 2, "D", nrhs=8, seed0=3)
     assert stats() == [320, 0, 0]
