@@ -6,6 +6,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/bdilu.h"
 #include "bdilu_kernels.h"
@@ -21,6 +22,7 @@ struct bdilu_ilu {
     int *d_flags = nullptr;
     size_t vec_cap = 0, flag_cap = 0;
     cudaStream_t st = nullptr;
+    int device = 0;  // the device the mirrors live on: every later call runs there, whatever the caller's current device
 };
 
 namespace {
@@ -45,9 +47,26 @@ int set_err(int code, const std::string &msg)
     return code;
 }
 
+// current device := dev for the lifetime of the guard (a handle / workspace may be used from a thread whose current
+// device is another one)
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
 void free_handle(bdilu_ilu *h)
 {
     if (!h) return;
+    DeviceGuard g(h->device);
     cudaFree(h->d_data); cudaFree(h->d_ipiv); cudaFree(h->d_rowbycol); cudaFree(h->d_colbyrow);
     cudaFree(h->d_info); cudaFree(h->d_b); cudaFree(h->d_x); cudaFree(h->d_flags);
     if (h->st) cudaStreamDestroy(h->st);
@@ -72,12 +91,18 @@ int bdilu_ilu_create(bdilu_ilu **out, double *host_data, int64_t sys_stride, int
     if (!h) return set_err(BDILU_ERR_ARG, "out of host memory");
     h->nsys = nsys; h->nblocks = nblocks; h->blockw = blockw; h->ndiag = ndiag; h->nsat = nsat; h->ld = ld;
     h->sys_stride = sys_stride;
+    if (cudaGetDevice(&h->device) != cudaSuccess) {
+        delete h;
+        cudaGetLastError();
+        return set_err(BDILU_ERR_CUDA, "cudaGetDevice failed");
+    }
     const size_t nbytes = sizeof(double) * (size_t)((int64_t)(nsys - 1) * sys_stride + nd);
     const size_t nidx = (size_t)nsys * nblocks * blockw;
 #define CUC(call)                                                                                      \
     do {                                                                                               \
         cudaError_t e_ = (call);                                                                       \
         if (e_ != cudaSuccess) {                                                                       \
+            if (h->st) cudaStreamSynchronize(h->st); /* nothing may still write the caller's memory */ \
             free_handle(h);                                                                            \
             cudaGetLastError();                                                                        \
             return set_err(BDILU_ERR_CUDA, std::string(#call ": ") + cudaGetErrorString(e_));          \
@@ -92,7 +117,7 @@ int bdilu_ilu_create(bdilu_ilu **out, double *host_data, int64_t sys_stride, int
     CUC(cudaMemcpyAsync(h->d_data, host_data, nbytes, cudaMemcpyHostToDevice, h->st));
     int rc = bdilu_factor(h->d_data, sys_stride, nsys, nblocks, blockw, ndiag, nsat, ld, h->d_ipiv, h->d_rowbycol,
                           h->d_colbyrow, h->d_info, h->st);
-    if (rc) { free_handle(h); return rc; }
+    if (rc) { cudaStreamSynchronize(h->st); free_handle(h); return rc; }
     if (copy_back) CUC(cudaMemcpyAsync(host_data, h->d_data, nbytes, cudaMemcpyDeviceToHost, h->st));
     if (ipiv) CUC(cudaMemcpyAsync(ipiv, h->d_ipiv, sizeof(int) * nidx, cudaMemcpyDeviceToHost, h->st));
     if (rowbycol) CUC(cudaMemcpyAsync(rowbycol, h->d_rowbycol, sizeof(int) * nidx, cudaMemcpyDeviceToHost, h->st));
@@ -107,6 +132,8 @@ int bdilu_ilu_create(bdilu_ilu **out, double *host_data, int64_t sys_stride, int
 int bdilu_ilu_solve(bdilu_ilu *h, const double *host_b, double *host_x, int nrhs, int *flags)
 {
     if (!h || !host_b || !host_x || nrhs < 1) return set_err(BDILU_ERR_ARG, "null handle/pointer or nrhs < 1");
+    DeviceGuard guard(h->device);
+    if (!guard.ok) return set_err(BDILU_ERR_CUDA, "cannot select the handle's device");
     const int64_t n = (int64_t)h->nblocks * h->blockw;
     const size_t nvec = (size_t)h->nsys * nrhs;
     const size_t vbytes = sizeof(double) * nvec * (size_t)n;
@@ -122,20 +149,34 @@ int bdilu_ilu_solve(bdilu_ilu *h, const double *host_b, double *host_x, int nrhs
         CUH(cudaMalloc(&h->d_flags, sizeof(int) * nvec));
         h->flag_cap = nvec;
     }
-    CUH(cudaMemcpyAsync(h->d_b, host_b, vbytes, cudaMemcpyHostToDevice, h->st));
-    int rc = bdilu_solve(h->d_data, h->sys_stride, h->nsys, h->nblocks, h->blockw, h->ndiag, h->nsat, h->ld,
-                         h->d_rowbycol, h->d_colbyrow, h->d_b, h->d_x, nrhs, n, n * nrhs, nullptr, h->d_flags, h->st);
-    if (rc) return rc;
-    CUH(cudaMemcpyAsync(host_x, h->d_x, vbytes, cudaMemcpyDeviceToHost, h->st));
-    int one = 0;
+    std::vector<int> own;  // flags when the caller does not want them (freed on every path)
     int *hf = flags;
-    int *tmp = nullptr;
-    if (!hf) hf = (nvec == 1) ? &one : (tmp = (int *)std::malloc(sizeof(int) * nvec));
-    CUH(cudaMemcpyAsync(hf, h->d_flags, sizeof(int) * nvec, cudaMemcpyDeviceToHost, h->st));
-    CUH(cudaStreamSynchronize(h->st));
+    if (!hf) {
+        try {
+            own.resize(nvec);
+        } catch (const std::bad_alloc &) {
+            return set_err(BDILU_ERR_ARG, "out of host memory");
+        }
+        hf = own.data();
+    }
+    // from here on copies into the caller's memory may be in flight: every exit goes through the synchronisation
+    int rc = BDILU_OK;
+    cudaError_t e = cudaMemcpyAsync(h->d_b, host_b, vbytes, cudaMemcpyHostToDevice, h->st);
+    if (e == cudaSuccess) {
+        rc = bdilu_solve(h->d_data, h->sys_stride, h->nsys, h->nblocks, h->blockw, h->ndiag, h->nsat, h->ld, h->d_rowbycol,
+                         h->d_colbyrow, h->d_b, h->d_x, nrhs, n, n * nrhs, nullptr, h->d_flags, h->st);
+        if (rc == BDILU_OK) e = cudaMemcpyAsync(host_x, h->d_x, vbytes, cudaMemcpyDeviceToHost, h->st);
+        if (rc == BDILU_OK && e == cudaSuccess)
+            e = cudaMemcpyAsync(hf, h->d_flags, sizeof(int) * nvec, cudaMemcpyDeviceToHost, h->st);
+    }
+    const cudaError_t es = cudaStreamSynchronize(h->st);
+    if (rc != BDILU_OK) return rc;
+    if (e != cudaSuccess || es != cudaSuccess) {
+        cudaGetLastError();
+        return set_err(BDILU_ERR_CUDA, std::string("bdilu_ilu_solve: ") + cudaGetErrorString(e != cudaSuccess ? e : es));
+    }
     int first = 0;
     for (size_t i = 0; i < nvec && !first; ++i) first = hf[i];
-    std::free(tmp);
     return first;
 }
 
@@ -199,8 +240,31 @@ struct Workspace {
     int *h_codes = nullptr;  // pinned staging for info + flags (see bdilu_host_factor_solve)
     size_t cap_data = 0, cap_vec = 0, cap_x = 0, cap_idx = 0, cap_info = 0, cap_flags = 0, cap_codes = 0;
     cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+    int device = -1;
+    void release()
+    {
+        if (device < 0) return;
+        DeviceGuard g(device);
+        cudaFree(d_data); cudaFree(d_b); cudaFree(d_x); cudaFree(d_idx); cudaFree(d_info); cudaFree(d_flags);
+        if (h_codes) cudaFreeHost(h_codes);
+        for (auto &s : st)
+            if (s) cudaStreamDestroy(s);
+        d_data = d_b = d_x = nullptr; d_idx = d_info = d_flags = nullptr; h_codes = nullptr;
+        cap_data = cap_vec = cap_x = cap_idx = cap_info = cap_flags = cap_codes = 0;
+        st[0] = st[1] = st[2] = nullptr;
+        cudaGetLastError();
+    }
 };
-Workspace g_ws;
+// one workspace per device (the mirrors of one device are useless on another), released when the library is unloaded
+constexpr int MAX_DEVICES = 64;
+struct Workspaces {
+    Workspace ws[MAX_DEVICES];
+    ~Workspaces()
+    {
+        for (auto &w : ws) w.release();
+    }
+};
+Workspaces g_wss;
 
 template <class T>
 cudaError_t grow(T *&p, size_t &cap, size_t want)
@@ -224,8 +288,22 @@ extern "C" int bdilu_host_factor_solve(const double *host_data, int64_t sys_stri
     if (ld == 0) ld = bdilu_default_ld(blockw);
     const int64_t nd = bdilu_ndata(nblocks, blockw, ndiag, nsat, ld), n = (int64_t)nblocks * blockw;
     if (nsys == 1) sys_stride = nd;
-    std::lock_guard<std::mutex> lock(g_ws.mu);
-    Workspace &W = g_ws;
+    int device = 0;
+    CUH(cudaGetDevice(&device));
+    if (device < 0 || device >= MAX_DEVICES) return set_err(BDILU_ERR_UNSUPPORTED, "device index out of range");
+    Workspace &W = g_wss.ws[device];
+    std::lock_guard<std::mutex> lock(W.mu);
+    W.device = device;
+    // Copies into the caller's memory run asynchronously on three streams: whatever happens below, nothing returns
+    // before those streams are drained (the workspace is reused by the next call, host_x belongs to the caller).
+    struct Drain {
+        Workspace &W;
+        ~Drain()
+        {
+            for (auto &s : W.st)
+                if (s) cudaStreamSynchronize(s);
+        }
+    } drain{W};
     for (auto &s : W.st)
         if (!s) CUH(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     // device copy is packed tight (stride nd) whatever the host stride

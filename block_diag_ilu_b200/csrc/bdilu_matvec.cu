@@ -67,7 +67,9 @@ __device__ __forceinline__ void row_dot(double (&acc)[NR], const double *__restr
     }
 }
 
-// MODE 0: out = A*vec.  MODE 1: norm2 += sum (b - A*x)^2 (vec = x, rhsb = b).  blockIdx.y = group of NR vectors.
+// MODE 0: out = A*vec.  MODE 1: out[(sys*nrhs + rhs)*gridDim.x + blockIdx.x] = this CTA's part of sum (b - A*x)^2
+// (vec = x, rhsb = b); norm2_finish_kernel adds the parts in a fixed order, so norms are bit-reproducible.
+// blockIdx.y = group of NR vectors.
 template <int MODE, int NR>
 __global__ void __launch_bounds__(MV_THREADS)
 matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const double *__restrict__ vec,
@@ -128,9 +130,24 @@ matvec_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D, const
         if (threadIdx.x < NR && rhs0 + threadIdx.x < V.nrhs) {
             double s = 0.0;
             for (int k = 0; k < MV_THREADS / 32; ++k) s += part[threadIdx.x][k];
-            atomicAdd(out + (int64_t)sys * V.nrhs + rhs0 + threadIdx.x, s);
+            out[((int64_t)sys * V.nrhs + rhs0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
         }
     }
+}
+
+// norm2[v] = sum of the `parts` partial sums of vector v, always in the same order: lane l adds parts l, l+32, ...
+// serially, then a fixed shuffle tree.  One warp per vector.
+__global__ void __launch_bounds__(128)
+norm2_finish_kernel(const double *__restrict__ partial, int parts, int64_t nvec, double *__restrict__ norm2)
+{
+    const int64_t v = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (v >= nvec) return;
+    const int lane = threadIdx.x & 31;
+    double s = 0.0;
+    for (int k = lane; k < parts; k += 32) s += partial[v * parts + k];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += group_bcast<32>(s, lane ^ off);
+    if (lane == 0) norm2[v] = s;
 }
 
 __global__ void __launch_bounds__(256)
@@ -154,18 +171,26 @@ scale_diag_add_kernel(double *dst, const double *src, int64_t dst_stride, int64_
     }
 }
 
+// grid.z / grid.y carry the system index: batches beyond 65535 systems go out in slabs
+constexpr int MAX_GRID_YZ = 65535;
+
 cudaError_t launch_dot_vec(const double *data, int64_t sys_stride, int nsys, const Dims &D,
                            const double *vec, double *out, const VecLayout &V, cudaStream_t st)
 {
     const int n = D.nblocks * D.w;
     if (n == 0 || nsys == 0 || V.nrhs == 0) return cudaSuccess;
-    if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
     const int nr = D.w > 64 ? 1 : (V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1));  // the staged slice is sized for blockw <= 64
-    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
-    if (nr == 8) matvec_kernel<0, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
-    else if (nr == 4) matvec_kernel<0, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
-    else matvec_kernel<0, 1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, vec, nullptr, out, V);
-    count_launch(1);
+    if ((V.nrhs + nr - 1) / nr > MAX_GRID_YZ) return cudaErrorInvalidValue;  // > 65535 groups of vectors per system
+    for (int s0 = 0; s0 < nsys; s0 += MAX_GRID_YZ) {
+        const int ns = nsys - s0 < MAX_GRID_YZ ? nsys - s0 : MAX_GRID_YZ;
+        const double *d0 = data + (int64_t)s0 * sys_stride, *v0 = vec + (int64_t)s0 * V.sys_stride;
+        double *o0 = out + (int64_t)s0 * V.sys_stride;
+        dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, ns);
+        if (nr == 8) matvec_kernel<0, 8><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, v0, nullptr, o0, V);
+        else if (nr == 4) matvec_kernel<0, 4><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, v0, nullptr, o0, V);
+        else matvec_kernel<0, 1><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, v0, nullptr, o0, V);
+        count_launch(1);
+    }
     return cudaGetLastError();
 }
 
@@ -175,27 +200,45 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
 {
     const int n = D.nblocks * D.w;
     if (nsys == 0 || V.nrhs == 0) return cudaSuccess;
-    if (V.nrhs > 65535 || nsys > 65535) return cudaErrorInvalidValue;
-    cudaError_t e = cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
-    if (e != cudaSuccess || n == 0) return e;
+    if (n == 0) return cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
     const int nr = D.w > 64 ? 1 : (V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1));  // the staged slice is sized for blockw <= 64
-    dim3 grid((n + MV_THREADS - 1) / MV_THREADS, (V.nrhs + nr - 1) / nr, nsys);
-    if (nr == 8) matvec_kernel<1, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
-    else if (nr == 4) matvec_kernel<1, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
-    else matvec_kernel<1, 1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, norm2, V);
-    count_launch(1);
-    return cudaGetLastError();
+    if ((V.nrhs + nr - 1) / nr > MAX_GRID_YZ) return cudaErrorInvalidValue;
+    const int gx = (n + MV_THREADS - 1) / MV_THREADS;
+    // one partial sum per (vector, CTA) in stream-ordered scratch, added up in a fixed order afterwards: no atomics, so
+    // the norms are bit-reproducible
+    const int slab = nsys < MAX_GRID_YZ ? nsys : MAX_GRID_YZ;
+    double *partial = nullptr;
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void **>(&partial), sizeof(double) * (size_t)slab * V.nrhs * gx, st);
+    if (e != cudaSuccess) return e;
+    for (int s0 = 0; s0 < nsys; s0 += MAX_GRID_YZ) {
+        const int ns = nsys - s0 < MAX_GRID_YZ ? nsys - s0 : MAX_GRID_YZ;
+        const double *d0 = data + (int64_t)s0 * sys_stride;
+        const double *b0 = b + (int64_t)s0 * V.sys_stride, *x0 = x + (int64_t)s0 * V.sys_stride;
+        dim3 grid(gx, (V.nrhs + nr - 1) / nr, ns);
+        if (nr == 8) matvec_kernel<1, 8><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, x0, b0, partial, V);
+        else if (nr == 4) matvec_kernel<1, 4><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, x0, b0, partial, V);
+        else matvec_kernel<1, 1><<<grid, MV_THREADS, 0, st>>>(d0, sys_stride, D, x0, b0, partial, V);
+        const int64_t nvec = (int64_t)ns * V.nrhs;
+        norm2_finish_kernel<<<(unsigned)((nvec + 3) / 4), 128, 0, st>>>(partial, gx, nvec, norm2 + (int64_t)s0 * V.nrhs);
+        count_launch(2);
+    }
+    e = cudaGetLastError();
+    cudaFreeAsync(partial, st);
+    return e;
 }
 
 cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, int nsys,
                                   const Dims &D, double scale, double diag_add, cudaStream_t st)
 {
     if (nsys == 0 || D.ndata == 0) return cudaSuccess;
-    if (nsys > 65535) return cudaErrorInvalidValue;
     const int64_t want = (D.ndata + 255) / 256;
-    dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), nsys);
-    scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst, src, dst_stride, src_stride, D, scale, diag_add);
-    count_launch(1);
+    for (int s0 = 0; s0 < nsys; s0 += MAX_GRID_YZ) {
+        const int ns = nsys - s0 < MAX_GRID_YZ ? nsys - s0 : MAX_GRID_YZ;
+        dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), ns);
+        scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst + (int64_t)s0 * dst_stride, src + (int64_t)s0 * src_stride, dst_stride,
+                                                    src_stride, D, scale, diag_add);
+        count_launch(1);
+    }
     return cudaGetLastError();
 }
 

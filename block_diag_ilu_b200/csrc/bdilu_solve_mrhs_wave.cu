@@ -455,6 +455,9 @@ bool try_launch_solve_mrhs_wave(int Q, const double *data, int64_t sys_stride, i
     *err = cudaSuccess;
     const int w = D.w;
     if (!(w == 8 || w == 16 || w == 32 || w == 64) || w < 2 * Q) return false;
+    // the progress word is (iteration << 8 | pairs) in an int32 and there are 2*nblocks iterations: longer chains go to
+    // the other kernels
+    if (D.nblocks >= (1 << 21)) return false;
     const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const Layout SL = make_layout(w, D.ld, D.ndiag);

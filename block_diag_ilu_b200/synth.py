@@ -5,13 +5,43 @@ diagonal and uniform(-1,1)*off_diag_factor couplings (scripts/ilu_vs_blocks.py:2
 python_prototype/demo.py:35-60).  Two families:
 
   "D"  dominant : blk ~ U(-1,1), blk[c,c] += sign(blk[c,c])*w ; sub,sup ~ 1e-3*U(-1,1)  (timed + parity)
-  "P"  pivoting : as D without the diagonal boost (about 87 % non-identity pivots at w=32; parity only)
+  "P"  pivoting : as D without the diagonal boost (about 87 % non-identity pivots at w=32; parity only).  Blocks in
+                  which two pivot candidates come within PIVOT_GAP relative at any elimination step are redrawn
+                  ("non-degenerate": a rounding difference between two correct eliminations must not flip a pivot)
+  "R"  permuted : a family-D block with its rows shuffled: every block pivots, and partial pivoting undoes the
+                  shuffle, so the chain is as well conditioned as D's (pivot parity at the full 1e-12 bar)
 
 Layout follows block_diag_ilu.hpp:99-102 (blocks | sub | sup | bot | top), ld >= blockw.
 """
 import numpy as np
 
 from .datastruct import ndata as _ndata
+
+
+PIVOT_GAP = 1e-10
+
+
+def min_pivot_gap(blk):
+    """Per block, the smallest relative gap between the two largest pivot candidates over all elimination steps of
+    LU with partial pivoting.  blk: [nblocks, w, w] column-major blocks ([b, c, r])."""
+    A = np.ascontiguousarray(np.transpose(blk, (0, 2, 1)))  # [b, r, c]
+    nb, w, _ = A.shape
+    gap = np.full(nb, np.inf)
+    idx = np.arange(nb)
+    for k in range(w - 1):
+        col = np.abs(A[:, k:, k])
+        part = np.partition(col, -2, axis=1)
+        top, second = part[:, -1], part[:, -2]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            gap = np.minimum(gap, np.where(top > 0, (top - second) / top, 0.0))
+        p = col.argmax(axis=1) + k
+        rk, rp = A[idx, k, :].copy(), A[idx, p, :].copy()
+        A[idx, k, :], A[idx, p, :] = rp, rk
+        piv = A[:, k, k]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            l = A[:, k + 1:, k] / piv[:, None]
+        A[:, k + 1:, k + 1:] -= l[:, :, None] * A[:, None, k, k + 1:]
+    return gap
 
 
 def make_system(nblocks, blockw, ndiag, family="D", seed=0, ld=None, nsat=0, coupling=1e-3):
@@ -24,8 +54,23 @@ def make_system(nblocks, blockw, ndiag, family="D", seed=0, ld=None, nsat=0, cou
         idx = np.arange(w)
         d = blk[:, idx, idx]
         blk[:, idx, idx] = d + np.where(d >= 0, 1.0, -1.0) * w
-    elif family != "P":
-        raise ValueError("family must be 'D' or 'P'")
+    elif family == "R":
+        idx = np.arange(w)
+        d = blk[:, idx, idx]
+        blk[:, idx, idx] = d + np.where(d >= 0, 1.0, -1.0) * w
+        prng = np.random.default_rng(7_000_003 * (seed + 1))
+        for bi in range(nblocks):
+            blk[bi] = blk[bi][:, prng.permutation(w)]  # rows of the column-major block [c, r]
+    elif family == "P":
+        if w > 1:
+            # redraw the (very rare) blocks with a near-tie between pivot candidates; the main stream is untouched
+            bad = np.nonzero(min_pivot_gap(blk) < PIVOT_GAP)[0]
+            redraw = np.random.default_rng(9_000_011 * (seed + 1))
+            while bad.size:
+                blk[bad] = redraw.uniform(-1.0, 1.0, size=(bad.size, w, w))
+                bad = bad[min_pivot_gap(blk[bad]) < PIVOT_GAP]
+    else:
+        raise ValueError("family must be 'D', 'P' or 'R'")
     n_all = _ndata(nblocks, blockw, ndiag, nsat, ld)
     data = np.zeros(n_all)
     nblk = nblocks * w * ld

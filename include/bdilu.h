@@ -25,6 +25,9 @@
  * cudaFreeAsync on the caller's stream).  Host entry points (bdilu_ilu_*, bdilu_host_*) take HOST pointers, own the device
  * mirrors, and block until the result is in host memory (the reference's calls are blocking).
  *
+ * Limits: blockw <= BDILU_MAX_BLOCKW; nblocks < 2^24; any number of systems; in bdilu_dot_vec / bdilu_residual_norm2
+ * at most 65535 groups of 8 vectors per system.  bdilu_residual_norm2 allocates stream-ordered scratch too.
+ *
  * Return value of every int function: 0 = ok, <0 = BDILU_ERR_* (see bdilu_last_error()).
  * There is no CPU fallback: without a CUDA device every compute entry point fails with
  * BDILU_ERR_CUDA.
@@ -114,7 +117,7 @@ BDILU_API int bdilu_dot_vec(const double *data, int64_t sys_stride, int nsys,
                   void *stream);
 
 /* New (not in the reference, built on dot_vec for validation): norm2[s*nrhs + r] = ||b - A x||_2^2
- * of the UNFACTORED matrix.  norm2 is zeroed by the call. */
+ * of the UNFACTORED matrix.  norm2 is overwritten; the sum is formed in a fixed order (bit-reproducible). */
 BDILU_API int bdilu_residual_norm2(const double *data, int64_t sys_stride, int nsys,
                          int nblocks, int blockw, int ndiag, int nsat, int ld,
                          const double *b, const double *x, int nrhs, int64_t rhs_stride,
