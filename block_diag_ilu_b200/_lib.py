@@ -24,6 +24,7 @@ _SIGNATURES = {
     "bdilu_factor_solve": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _p, _p, _p, _p, _i, _i64, _i64, _p, _p]),
     "bdilu_dot_vec": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _i64, _i64, _p]),
     "bdilu_residual_norm2": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _i64, _i64, _p, _p]),
+    "bdilu_residual_norm2_static": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _i64, _i64, _p, _p]),
     "bdilu_scale_diag_add": (_i, [_p, _p, _i64, _i] + _DIMS + [_d, _d, _p]),
     "bdilu_factor_scaled": (_i, [_p, _i64, _p, _i64, _i] + _DIMS + [_d, _d, _p, _p, _p, _p, _p]),
     "bdilu_workspace_bytes": (C.c_size_t, [_i] + _DIMS + [_i]),

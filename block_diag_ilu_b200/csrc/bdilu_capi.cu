@@ -191,6 +191,29 @@ int bdilu_residual_norm2(const double *data, int64_t sys_stride, int nsys, int n
     return BDILU_OK;
 }
 
+int bdilu_residual_norm2_static(const double *data, int64_t sys_stride, int nsys, int nblocks, int blockw, int ndiag,
+                                int nsat, int ld, const double *b, const double *x, int nrhs, int64_t rhs_stride,
+                                int64_t sys_rhs_stride, double *norm2, void *stream)
+{
+    Dims D;
+    int rc = check_dims(nsys, sys_stride, nblocks, blockw, ndiag, nsat, ld, D);
+    if (rc) return rc;
+    if ((rc = check_vecs(D, nsys, nrhs, rhs_stride, sys_rhs_stride))) return rc;
+    if (nsys == 0 || nrhs == 0) return BDILU_OK;
+    if (!data || !b || !x || !norm2) return fail(BDILU_ERR_ARG, "null pointer");
+    VecLayout V{nrhs, rhs_stride, sys_rhs_stride};
+    if (residual_norm2_static_partials(nsys, D, V) > BDILU_STATIC_NORM2_PARTIALS) {
+        char msg[200];
+        snprintf(msg, sizeof msg,
+                 "bdilu_residual_norm2_static: nsys*nrhs*ceil(nblocks*blockw/128) = %lld exceeds the static scratch of %d "
+                 "partial sums; use bdilu_residual_norm2",
+                 (long long)residual_norm2_static_partials(nsys, D, V), BDILU_STATIC_NORM2_PARTIALS);
+        return fail(BDILU_ERR_UNSUPPORTED, msg);
+    }
+    CU(launch_residual_norm2_static(data, sys_stride, nsys, D, b, x, V, norm2, (cudaStream_t)stream));
+    return BDILU_OK;
+}
+
 int bdilu_scale_diag_add(double *dst, const double *src, int64_t sys_stride, int nsys, int nblocks, int blockw,
                          int ndiag, int nsat, int ld, double scale, double diag_add, void *stream)
 {

@@ -65,6 +65,12 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
                                   const double *b, const double *x, const VecLayout &V, double *norm2,
                                   cudaStream_t st);
 
+// the same with the partial sums in a file-scope device array: no allocation of any kind (bdilu_residual_norm2_static)
+int64_t residual_norm2_static_partials(int nsys, const Dims &D, const VecLayout &V);
+cudaError_t launch_residual_norm2_static(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                                         const double *b, const double *x, const VecLayout &V, double *norm2,
+                                         cudaStream_t st);
+
 cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, int nsys,
                                   const Dims &D, double scale, double diag_add, cudaStream_t st);
 

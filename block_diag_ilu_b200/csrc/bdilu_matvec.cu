@@ -6,6 +6,9 @@
 // contiguous 8*blockw-byte segment.  The reference scatters sub/sup/top/bot contributions into
 // `out`; here each row gathers the (at most 2*ndiag + satellite) couplings that land on it, so no
 // zero-fill pass and no atomics are needed.
+#include <mutex>
+
+#include "../../include/bdilu.h"
 #include "bdilu_common.cuh"
 #include "bdilu_kernels.h"
 
@@ -225,6 +228,68 @@ cudaError_t launch_residual_norm2(const double *data, int64_t sys_stride, int ns
     e = cudaGetLastError();
     cudaFreeAsync(partial, st);
     return e;
+}
+
+// ---- residual norms without any allocation (bdilu_residual_norm2_static, include/bdilu.h) -------------------------------
+// The per-CTA partial sums go to a file-scope device array instead of stream-ordered scratch, for callers that may not
+// allocate (CUDA graph capture, serving loops).  Every device that loads the library holds the array until exit.  All
+// calls share it: calls that overlap on one GPU (two streams, two threads) race.  The kernels overwrite every slot they
+// later read, so nothing has to start at zero and the previous call's contents are harmless.
+constexpr int64_t STATIC_PARTIALS = BDILU_STATIC_NORM2_PARTIALS;  // doubles: 1 MiB per device
+static __device__ __align__(256) double g_norm2_partials[STATIC_PARTIALS];
+
+// The array's name is only a host-side stand-in in host code; its device address is looked up once per device, with
+// that device current.
+static constexpr int MAX_DEVICES = 64;
+static double *g_partials_addr[MAX_DEVICES];
+static std::mutex g_partials_mutex;
+
+static cudaError_t static_partials(double **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_partials_mutex);
+    if (!g_partials_addr[dev]) {
+        double *p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_norm2_partials);
+        if (e != cudaSuccess) return e;
+        g_partials_addr[dev] = p;
+    }
+    *out = g_partials_addr[dev];
+    return cudaSuccess;
+}
+
+int64_t residual_norm2_static_partials(int nsys, const Dims &D, const VecLayout &V)
+{
+    const int64_t n = (int64_t)D.nblocks * D.w;
+    return (int64_t)nsys * V.nrhs * ((n + MV_THREADS - 1) / MV_THREADS);
+}
+
+cudaError_t launch_residual_norm2_static(const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                                         const double *b, const double *x, const VecLayout &V, double *norm2,
+                                         cudaStream_t st)
+{
+    const int n = D.nblocks * D.w;
+    if (nsys == 0 || V.nrhs == 0) return cudaSuccess;
+    if (n == 0) return cudaMemsetAsync(norm2, 0, sizeof(double) * (size_t)nsys * V.nrhs, st);
+    const int nr = D.w > 64 ? 1 : (V.nrhs >= 8 ? 8 : (V.nrhs >= 4 ? 4 : 1));
+    // one launch covers the batch (the caller checked the partial-sum count, which bounds nsys far below 65535)
+    if (nsys > MAX_GRID_YZ || (V.nrhs + nr - 1) / nr > MAX_GRID_YZ) return cudaErrorInvalidValue;
+    if (residual_norm2_static_partials(nsys, D, V) > STATIC_PARTIALS) return cudaErrorInvalidValue;
+    double *partial = nullptr;
+    cudaError_t e = static_partials(&partial);
+    if (e != cudaSuccess) return e;
+    const int gx = (n + MV_THREADS - 1) / MV_THREADS;
+    dim3 grid(gx, (V.nrhs + nr - 1) / nr, nsys);
+    if (nr == 8) matvec_kernel<1, 8><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, partial, V);
+    else if (nr == 4) matvec_kernel<1, 4><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, partial, V);
+    else matvec_kernel<1, 1><<<grid, MV_THREADS, 0, st>>>(data, sys_stride, D, x, b, partial, V);
+    const int64_t nvec = (int64_t)nsys * V.nrhs;
+    norm2_finish_kernel<<<(unsigned)((nvec + 3) / 4), 128, 0, st>>>(partial, gx, nvec, norm2);
+    count_launch(2);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_stride, int64_t src_stride, int nsys,

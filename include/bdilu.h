@@ -123,6 +123,21 @@ BDILU_API int bdilu_residual_norm2(const double *data, int64_t sys_stride, int n
                          const double *b, const double *x, int nrhs, int64_t rhs_stride,
                          int64_t sys_rhs_stride, double *norm2, void *stream);
 
+/* bdilu_residual_norm2 without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results (bit-identical) as bdilu_residual_norm2, but the per-CTA partial sums
+ * live in a file-scope device array of BDILU_STATIC_NORM2_PARTIALS doubles (1 MiB, held by every GPU that loads the
+ * library until exit) instead of stream-ordered scratch, and the call makes no cudaMalloc / cudaFree / cudaMallocAsync
+ * of any kind.  Limit: nsys * nrhs * ceil(nblocks*blockw / 128) <= BDILU_STATIC_NORM2_PARTIALS, otherwise
+ * BDILU_ERR_UNSUPPORTED with a message naming both numbers.  Every call on a device shares the one array: calls that
+ * overlap on the GPU (different streams or threads without ordering between them) race; calls ordered on one stream are
+ * safe.  Nothing in the array needs to start at zero (every slot read is written by the same call first). */
+#define BDILU_STATIC_NORM2_PARTIALS 131072
+BDILU_API int bdilu_residual_norm2_static(const double *data, int64_t sys_stride, int nsys,
+                                int nblocks, int blockw, int ndiag, int nsat, int ld,
+                                const double *b, const double *x, int nrhs, int64_t rhs_stride,
+                                int64_t sys_rhs_stride, double *norm2, void *stream);
+
 /* BlockDiagMatrix<double>::scale_diag_add(source, scale, diag_add)  (block_diag_ilu.hpp:276-287;
  * set_to_eye_plus_scaled_mtx(scale, source) == scale_diag_add(source, scale, 1), :288-290):
  * dst = scale*src, then diag_add added to every diagonal element of every block.  dst may equal src. */
