@@ -34,6 +34,17 @@ _SIGNATURES = {
     "bdilu_host_dot_vec": (_i, [_p] + _DIMS + [_p, _p, _i]),
     "bdilu_host_scale_diag_add": (_i, [_p, _p] + _DIMS + [_d, _d]),
     "bdilu_host_factor_solve": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _p, _p]),
+    "bdilu_default_ld_f32": (_i, [_i]),
+    "bdilu_factor_f32": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _p, _p, _p]),
+    "bdilu_solve_f32": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _p, _p, _i, _i64, _i64, _p, _p]),
+    "bdilu_factor_solve_f32": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _p, _p, _p, _p, _i, _i64, _i64, _p, _p]),
+    "bdilu_dot_vec_f32": (_i, [_p, _i64, _i] + _DIMS + [_p, _p, _i, _i64, _i64, _p]),
+    "bdilu_scale_diag_add_f32": (_i, [_p, _p, _i64, _i] + _DIMS + [C.c_float, C.c_float, _p]),
+    "bdilu_ilu_create_f32": (_i, [C.POINTER(_p), _p, _i64, _i] + _DIMS + [_i, _p, _p, _p, _p]),
+    "bdilu_ilu_solve_f32": (_i, [_p, _p, _p, _i, _p]),
+    "bdilu_ilu_destroy_f32": (None, [_p]),
+    "bdilu_host_dot_vec_f32": (_i, [_p] + _DIMS + [_p, _p, _i]),
+    "bdilu_host_scale_diag_add_f32": (_i, [_p, _p] + _DIMS + [C.c_float, C.c_float]),
     "bdilu_launch_count": (_i64, []),
     "bdilu_launch_count_reset": (None, []),
 }

@@ -46,11 +46,12 @@ int cuda_fail(cudaError_t e, const char *where)
         if (e_ != cudaSuccess) return cuda_fail(e_, #call);    \
     } while (0)
 
-int check_dims(int nsys, int64_t sys_stride, int nblocks, int blockw, int ndiag, int nsat, int &ld, Dims &D)
+int check_dims(int nsys, int64_t sys_stride, int nblocks, int blockw, int ndiag, int nsat, int &ld, Dims &D,
+               int esize = (int)sizeof(double))
 {
     if (nsys < 0 || nblocks < 0 || blockw < 1 || ndiag < 0 || nsat < 0 || ld < 0)
         return fail(BDILU_ERR_ARG, "negative dimension or blockw < 1");
-    if (ld == 0) ld = bdilu_default_ld(blockw);
+    if (ld == 0) ld = esize == 4 ? bdilu_default_ld_f32(blockw) : bdilu_default_ld(blockw);
     if (ld < blockw) return fail(BDILU_ERR_ARG, "ld < blockw");
     if (nblocks > 0 && (ndiag > nblocks - 1 && ndiag > 0)) return fail(BDILU_ERR_ARG, "ndiag > nblocks - 1");
     if (nsat > nblocks) return fail(BDILU_ERR_ARG, "nsat > nblocks");
@@ -73,6 +74,20 @@ int check_vecs(const Dims &D, int nsys, int nrhs, int64_t rhs_stride, int64_t sy
 
 }  // namespace
 
+// the same argument checks and error channel for the other translation units with entry points (bdilu_f32.cu)
+namespace bdilu {
+int api_check_dims(int nsys, int64_t sys_stride, int nblocks, int blockw, int ndiag, int nsat, int &ld, Dims &D, int esize)
+{
+    return check_dims(nsys, sys_stride, nblocks, blockw, ndiag, nsat, ld, D, esize);
+}
+int api_check_vecs(const Dims &D, int nsys, int nrhs, int64_t rhs_stride, int64_t sys_rhs_stride)
+{
+    return check_vecs(D, nsys, nrhs, rhs_stride, sys_rhs_stride);
+}
+int api_fail(int code, const char *msg) { return fail(code, msg); }
+int api_cuda_fail(cudaError_t e, const char *where) { return cuda_fail(e, where); }
+}  // namespace bdilu
+
 extern "C" {
 
 int bdilu_version(void) { return BDILU_VERSION; }
@@ -91,6 +106,11 @@ int bdilu_device_count(void)
 int bdilu_default_ld(int blockw)
 {
     return (int)((((size_t)blockw * sizeof(double) + 63) & ~(size_t)63) / sizeof(double));
+}
+
+int bdilu_default_ld_f32(int blockw)
+{
+    return (int)((((size_t)blockw * sizeof(float) + 63) & ~(size_t)63) / sizeof(float));
 }
 
 int64_t bdilu_ndata(int nblocks, int blockw, int ndiag, int nsat, int ld)

@@ -10,11 +10,19 @@ namespace bdilu {
 void count_launch(int n);
 void set_last_error(const char *msg);  // feeds bdilu_last_error() on the calling thread
 
+// argument checks / error channel of the C ABI, shared by the translation units that hold entry points
+struct Dims;
+int api_check_dims(int nsys, int64_t sys_stride, int nblocks, int blockw, int ndiag, int nsat, int &ld, Dims &D, int esize);
+int api_fail(int code, const char *msg);
+int api_cuda_fail(cudaError_t e, const char *where);
+
 // strides of right-hand-side / solution vectors (in doubles)
 struct VecLayout {
     int nrhs;
     int64_t rhs_stride, sys_stride;
 };
+
+int api_check_vecs(const Dims &D, int nsys, int nrhs, int64_t rhs_stride, int64_t sys_rhs_stride);
 
 cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
                           int *rowbycol, int *colbyrow, int *info, cudaStream_t st);

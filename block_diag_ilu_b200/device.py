@@ -3,7 +3,8 @@
 PyTorch is plumbing here (HBM allocations, streams); every operation is one call into the C ABI
 (include/bdilu.h) on raw device pointers.  Shapes:
 
-    data  float64 [nsys, ndata]     one packed BlockDiagMatrix::m_data per row (block_diag_ilu.hpp:99-102)
+    data  float64 [nsys, ndata]     (float32 tensors take the *_f32 entry points: factor, solve, dot_vec, scale_diag_add)
+                                    one packed BlockDiagMatrix::m_data per row (block_diag_ilu.hpp:99-102)
     b, x  float64 [nsys, nrhs, n]   n = nblocks*blockw  ([nsys, n] and [n] are accepted and restored)
     ipiv, rowbycol, colbyrow  int32 [nsys, n];  info int32 [nsys];  flags int32 [nsys, nrhs]
 """
@@ -31,8 +32,8 @@ class Shape:
 
 
 def _check_data(data, shape):
-    if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype == torch.float64):
-        raise TypeError("data must be a CUDA float64 tensor")
+    if not (isinstance(data, torch.Tensor) and data.is_cuda and data.dtype in (torch.float64, torch.float32)):
+        raise TypeError("data must be a CUDA float64 (or float32: the *_f32 entry points) tensor")
     if data.dim() == 1:
         data = data.unsqueeze(0)
     if data.dim() != 2 or data.shape[1] < shape.ndata or data.stride(1) != 1:
@@ -40,10 +41,10 @@ def _check_data(data, shape):
     return data
 
 
-def _vec3(v, nsys, n):
+def _vec3(v, nsys, n, dtype=torch.float64):
     """-> ([nsys, nrhs, n] contiguous view/copy, restore-shape)"""
-    if not (isinstance(v, torch.Tensor) and v.is_cuda and v.dtype == torch.float64):
-        raise TypeError("vectors must be CUDA float64 tensors")
+    if not (isinstance(v, torch.Tensor) and v.is_cuda and v.dtype == dtype):
+        raise TypeError("vectors must be CUDA %s tensors" % str(dtype).replace("torch.", ""))
     shp = v.shape
     if v.dim() == 1:
         v = v.view(1, 1, -1)
@@ -75,8 +76,9 @@ class BatchedILU:
         self.colbyrow = torch.empty_like(self.ipiv)
         self.info = torch.empty((self.nsys,), dtype=torch.int32, device=dev)
         self.flags = None
+        factor = _lib.lib().bdilu_factor_f32 if self.data.dtype == torch.float32 else _lib.lib().bdilu_factor
         with torch.cuda.device(dev):
-            _lib.check(_lib.lib().bdilu_factor(
+            _lib.check(factor(
                 _lib.ptr(self.data), self.data.stride(0), self.nsys, *self.shape.dims(),
                 _lib.ptr(self.ipiv), _lib.ptr(self.rowbycol), _lib.ptr(self.colbyrow), _lib.ptr(self.info),
                 _stream()))
@@ -95,6 +97,8 @@ class BatchedILU:
         self = cls.__new__(cls)
         self.shape = Shape(nblocks, blockw, ndiag, nsat, ld)
         src = _check_data(src, self.shape)
+        if src.dtype != torch.float64:
+            raise TypeError("from_scaled: the fused assembly is float64 only")
         self.data = torch.empty_like(src) if out is None else _check_data(out, self.shape)
         if self.data.shape[0] != src.shape[0]:
             raise ValueError("out must hold as many systems as src")
@@ -117,15 +121,19 @@ class BatchedILU:
 
     def solve(self, b, out=None):
         """x with the shape of b; per-vector reference return codes land in self.flags [nsys, nrhs]."""
-        b3, shp = _vec3(b, self.nsys, self.shape.n)
+        dt = self.data.dtype
+        b3, shp = _vec3(b, self.nsys, self.shape.n, dt)
         nrhs = b3.shape[1]
-        x3 = torch.empty_like(b3) if out is None else _vec3(out, self.nsys, self.shape.n)[0]
+        x3 = torch.empty_like(b3) if out is None else _vec3(out, self.nsys, self.shape.n, dt)[0]
         self.flags = torch.empty((self.nsys, nrhs), dtype=torch.int32, device=b3.device)
-        with torch.cuda.device(b3.device):
-            _lib.check(_lib.lib().bdilu_solve(
-                _lib.ptr(self.data), self.data.stride(0), self.nsys, *self.shape.dims(),
+        head = (_lib.ptr(self.data), self.data.stride(0), self.nsys, *self.shape.dims(),
                 _lib.ptr(self.rowbycol), _lib.ptr(self.colbyrow), _lib.ptr(b3), _lib.ptr(x3),
-                nrhs, self.shape.n, self.shape.n * nrhs, None, _lib.ptr(self.flags), _stream()))
+                nrhs, self.shape.n, self.shape.n * nrhs)
+        with torch.cuda.device(b3.device):
+            if dt == torch.float32:
+                _lib.check(_lib.lib().bdilu_solve_f32(*head, _lib.ptr(self.flags), _stream()))
+            else:
+                _lib.check(_lib.lib().bdilu_solve(*head, None, _lib.ptr(self.flags), _stream()))
         return x3.view(shp)
 
 
@@ -137,7 +145,7 @@ def factor_solve(data, b, nblocks, blockw, ndiag, nsat=0, ld=None):
     ilu.data = _check_data(data, ilu.shape)
     ilu.nsys = ilu.data.shape[0]
     dev, n = ilu.data.device, ilu.shape.n
-    b3, shp = _vec3(b, ilu.nsys, n)
+    b3, shp = _vec3(b, ilu.nsys, n, ilu.data.dtype)
     nrhs = b3.shape[1]
     ilu.ipiv = torch.empty((ilu.nsys, n), dtype=torch.int32, device=dev)
     ilu.rowbycol = torch.empty_like(ilu.ipiv)
@@ -145,8 +153,9 @@ def factor_solve(data, b, nblocks, blockw, ndiag, nsat=0, ld=None):
     ilu.info = torch.empty((ilu.nsys,), dtype=torch.int32, device=dev)
     ilu.flags = torch.empty((ilu.nsys, nrhs), dtype=torch.int32, device=dev)
     x3 = torch.empty_like(b3)
+    fs = _lib.lib().bdilu_factor_solve_f32 if ilu.data.dtype == torch.float32 else _lib.lib().bdilu_factor_solve
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().bdilu_factor_solve(
+        _lib.check(fs(
             _lib.ptr(ilu.data), ilu.data.stride(0), ilu.nsys, *ilu.shape.dims(),
             _lib.ptr(ilu.ipiv), _lib.ptr(ilu.rowbycol), _lib.ptr(ilu.colbyrow), _lib.ptr(ilu.info),
             _lib.ptr(b3), _lib.ptr(x3), nrhs, n, n * nrhs, _lib.ptr(ilu.flags), _stream()))
@@ -166,6 +175,8 @@ class GraphedFactorSolve:
         _lib.require_device()
         self.shape = Shape(nblocks, blockw, ndiag, nsat, ld)
         self.a = _check_data(a, self.shape)
+        if self.a.dtype != torch.float64:
+            raise TypeError("GraphedFactorSolve is float64 only")
         self.nsys = self.a.shape[0]
         dev, n = self.a.device, self.shape.n
         self.b, self._shp = _vec3(b, self.nsys, n)
@@ -206,10 +217,11 @@ def dot_vec(data, vec, nblocks, blockw, ndiag, nsat=0, ld=None, out=None):
     _lib.require_device()
     shape = Shape(nblocks, blockw, ndiag, nsat, ld)
     data = _check_data(data, shape)
-    v3, shp = _vec3(vec, data.shape[0], shape.n)
-    out = torch.empty_like(v3) if out is None else _vec3(out, data.shape[0], shape.n)[0]
+    v3, shp = _vec3(vec, data.shape[0], shape.n, data.dtype)
+    out = torch.empty_like(v3) if out is None else _vec3(out, data.shape[0], shape.n, data.dtype)[0]
+    mv = _lib.lib().bdilu_dot_vec_f32 if data.dtype == torch.float32 else _lib.lib().bdilu_dot_vec
     with torch.cuda.device(data.device):
-        _lib.check(_lib.lib().bdilu_dot_vec(
+        _lib.check(mv(
             _lib.ptr(data), data.stride(0), data.shape[0], *shape.dims(), _lib.ptr(v3), _lib.ptr(out),
             v3.shape[1], shape.n, shape.n * v3.shape[1], _stream()))
     return out.view(shp)
@@ -220,6 +232,8 @@ def residual_norm2(data, b, x, nblocks, blockw, ndiag, nsat=0, ld=None):
     _lib.require_device()
     shape = Shape(nblocks, blockw, ndiag, nsat, ld)
     data = _check_data(data, shape)
+    if data.dtype != torch.float64:
+        raise TypeError("residual_norm2 is float64 only")
     b3, _ = _vec3(b, data.shape[0], shape.n)
     x3, _ = _vec3(x, data.shape[0], shape.n)
     out = torch.empty((data.shape[0], b3.shape[1]), dtype=torch.float64, device=data.device)
@@ -236,8 +250,9 @@ def scale_diag_add(src, scale, diag_add, nblocks, blockw, ndiag, nsat=0, ld=None
     shape = Shape(nblocks, blockw, ndiag, nsat, ld)
     src = _check_data(src, shape)
     dst = torch.empty_like(src) if out is None else _check_data(out, shape)
+    sda = _lib.lib().bdilu_scale_diag_add_f32 if src.dtype == torch.float32 else _lib.lib().bdilu_scale_diag_add
     with torch.cuda.device(src.device):
-        _lib.check(_lib.lib().bdilu_scale_diag_add(
+        _lib.check(sda(
             _lib.ptr(dst), _lib.ptr(src), src.stride(0), src.shape[0], *shape.dims(),
             float(scale), float(diag_add), _stream()))
     return dst

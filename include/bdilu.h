@@ -194,6 +194,52 @@ BDILU_API int bdilu_host_factor_solve(const double *host_data, int64_t sys_strid
                             int nblocks, int blockw, int ndiag, int nsat, int ld,
                             const double *host_b, double *host_x, int nrhs, int *info, int *flags);
 
+/* ---- Real_t = float ---------------------------------------------------------------------------------------------
+ * The reference's classes are templates over Real_t (block_diag_ilu.hpp:63, 104, 426; float build of its tests:
+ * tests/test_block_diag.cpp:649-712; LAPACK side sgetrf_, anyode_blas_lapack.hpp:56).  The *_f32 entry points are the
+ * float instantiation: the same packed layout with float elements (default ld = blockw rounded up to 64 BYTES, i.e. to
+ * a multiple of 16 floats: bdilu_default_ld_f32; bdilu_ndata(..., ld) counts elements whatever their type), the same
+ * int32 index arrays, info words and solve flags, the same argument meaning and error codes as their double
+ * namesakes above.  Kernels: csrc/bdilu_f32.cu (one lane group per block / per vector; the wavefront and many-vector
+ * solve kernels are double-only). */
+BDILU_API int bdilu_default_ld_f32(int blockw);
+/* ILU_inplace<float>::ILU_inplace(view)  (block_diag_ilu.hpp:430-485) */
+BDILU_API int bdilu_factor_f32(float *data, int64_t sys_stride, int nsys,
+                     int nblocks, int blockw, int ndiag, int nsat, int ld,
+                     int *ipiv, int *rowbycol, int *colbyrow, int *info, void *stream);
+/* ILU_inplace<float>::solve(b, x)  (block_diag_ilu.hpp:486-538) */
+BDILU_API int bdilu_solve_f32(const float *data, int64_t sys_stride, int nsys,
+                    int nblocks, int blockw, int ndiag, int nsat, int ld,
+                    const int *rowbycol, const int *colbyrow,
+                    const float *b, float *x, int nrhs, int64_t rhs_stride, int64_t sys_rhs_stride,
+                    int *flags, void *stream);
+/* ILU<float>(A) + solve(b, x)  (block_diag_ilu.hpp:541-551), in place, back to back on `stream` */
+BDILU_API int bdilu_factor_solve_f32(float *data, int64_t sys_stride, int nsys,
+                           int nblocks, int blockw, int ndiag, int nsat, int ld,
+                           int *ipiv, int *rowbycol, int *colbyrow, int *info,
+                           const float *b, float *x, int nrhs, int64_t rhs_stride, int64_t sys_rhs_stride,
+                           int *flags, void *stream);
+/* BlockDiagMatrix<float>::dot_vec  (block_diag_ilu.hpp:295-326); at most 65535 vectors per system */
+BDILU_API int bdilu_dot_vec_f32(const float *data, int64_t sys_stride, int nsys,
+                      int nblocks, int blockw, int ndiag, int nsat, int ld,
+                      const float *vec, float *out, int nrhs, int64_t rhs_stride, int64_t sys_rhs_stride,
+                      void *stream);
+/* BlockDiagMatrix<float>::scale_diag_add  (block_diag_ilu.hpp:276-287) */
+BDILU_API int bdilu_scale_diag_add_f32(float *dst, const float *src, int64_t sys_stride, int nsys,
+                             int nblocks, int blockw, int ndiag, int nsat, int ld,
+                             float scale, float diag_add, void *stream);
+/* host forms, as bdilu_ilu_create / bdilu_ilu_solve / bdilu_ilu_destroy / bdilu_host_dot_vec / bdilu_host_scale_diag_add */
+typedef struct bdilu_ilu_f32 bdilu_ilu_f32;
+BDILU_API int bdilu_ilu_create_f32(bdilu_ilu_f32 **out, float *host_data, int64_t sys_stride, int nsys,
+                         int nblocks, int blockw, int ndiag, int nsat, int ld, int copy_back,
+                         int *ipiv, int *rowbycol, int *colbyrow, int *info);
+BDILU_API int bdilu_ilu_solve_f32(bdilu_ilu_f32 *h, const float *host_b, float *host_x, int nrhs, int *flags);
+BDILU_API void bdilu_ilu_destroy_f32(bdilu_ilu_f32 *h);
+BDILU_API int bdilu_host_dot_vec_f32(const float *host_data, int nblocks, int blockw, int ndiag, int nsat, int ld,
+                           const float *host_vec, float *host_out, int nrhs);
+BDILU_API int bdilu_host_scale_diag_add_f32(float *host_dst, const float *host_src, int nblocks, int blockw,
+                                  int ndiag, int nsat, int ld, float scale, float diag_add);
+
 /* Kernels launched by this library since load / last reset (bench.py's gpu_launches claim). */
 BDILU_API int64_t bdilu_launch_count(void);
 BDILU_API void bdilu_launch_count_reset(void);

@@ -209,6 +209,74 @@ class Ref:
         return dict(seconds=float(secs), ipiv=ipiv, rowbycol=rbc, colbyrow=cbr, x=x, infos=infos)
 
 
+class RefF32:
+    """The reference header instantiated with Real_t = float (sgetrf).  Same interface as Ref on float32 buffers."""
+    kind = "reference-f32"
+
+    def __init__(self, path=None):
+        path = path or os.path.join(HERE, "_ref", "libbdilu_ref.so")
+        if not os.path.exists(path):
+            from . import build_oracle
+            path = build_oracle.build_ref(verbose=False)
+            if path is None:
+                raise FileNotFoundError("oracle/_ref/libbdilu_ref.so missing and /root/reference absent")
+        fp = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+        L = self.lib = C.CDLL(path)
+        L.ref_ndata_f32.restype = C.c_int64
+        L.ref_ndata_f32.argtypes = [C.c_int] * 5
+        L.ref_default_ld_f32.argtypes = [C.c_int]
+        L.ref_ilu_create_f32.restype = C.c_void_p
+        L.ref_ilu_create_f32.argtypes = [fp] + [C.c_int] * 5 + [_ip, _ip, _ip, C.POINTER(C.c_int)]
+        L.ref_ilu_solve_f32.argtypes = [C.c_void_p, fp, fp]
+        L.ref_ilu_destroy_f32.argtypes = [C.c_void_p]
+        L.ref_dot_vec_f32.argtypes = [fp] + [C.c_int] * 5 + [fp, fp]
+        L.ref_scale_diag_add_f32.argtypes = [fp, fp] + [C.c_int] * 5 + [C.c_float, C.c_float]
+        self._handles = {}
+
+    def ndata(self, nblocks, blockw, ndiag, nsat=0, ld=0):
+        return int(self.lib.ref_ndata_f32(nblocks, blockw, ndiag, nsat, ld))
+
+    def default_ld(self, blockw):
+        return int(self.lib.ref_default_ld_f32(blockw))
+
+    def factor(self, data, nblocks, blockw, ndiag, nsat, ld):
+        assert data.dtype == np.float32
+        n = nblocks * blockw
+        ipiv, rbc, cbr = (np.zeros(n, np.int32) for _ in range(3))
+        threw = C.c_int(0)
+        h = self.lib.ref_ilu_create_f32(data, nblocks, blockw, ndiag, nsat, ld, ipiv, rbc, cbr, C.byref(threw))
+        key = data.ctypes.data
+        old = self._handles.pop(key, None)
+        if old:
+            self.lib.ref_ilu_destroy_f32(old[0])
+        if h:
+            self._handles[key] = (h, data)
+        return ipiv, rbc, cbr, (-1 if threw.value else 0)
+
+    def solve(self, data, nblocks, blockw, ndiag, nsat, ld, rowbycol, colbyrow, b):
+        h = self._handles[data.ctypes.data][0]
+        b = np.ascontiguousarray(b, np.float32)
+        x = np.zeros_like(b)
+        flag = self.lib.ref_ilu_solve_f32(h, b, x)
+        return x, int(flag)
+
+    def dot_vec(self, data, nblocks, blockw, ndiag, nsat, ld, vec):
+        vec = np.ascontiguousarray(vec, np.float32)
+        out = np.full_like(vec, np.nan)
+        self.lib.ref_dot_vec_f32(data, nblocks, blockw, ndiag, nsat, ld, vec, out)
+        return out
+
+    def scale_diag_add(self, src, nblocks, blockw, ndiag, nsat, ld, scale, diag_add):
+        dst = np.empty_like(src)
+        self.lib.ref_scale_diag_add_f32(dst, src, nblocks, blockw, ndiag, nsat, ld, scale, diag_add)
+        return dst
+
+    def release(self):
+        for h, _ in self._handles.values():
+            self.lib.ref_ilu_destroy_f32(h)
+        self._handles.clear()
+
+
 def best():
     """The reference when its compiled shim is available (here, or prebuilt on the GPU box), else the port."""
     try:

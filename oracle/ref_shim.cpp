@@ -162,3 +162,62 @@ EXPORT double ref_factor_solve_batch(double *data, int64_t sys_stride, int nsys,
     }
     return now() - t0;
 }
+
+// ---- Real_t = float: the same header instantiated with float (sgetrf through AnyODE::getrf_callback<float>,
+// anyode_blas_lapack.hpp:56) ----------------------------------------------------------------------------------------
+namespace {
+struct RefILUf {
+    std::unique_ptr<BlockDiagMatrix<float>> view;
+    std::unique_ptr<ILU_inplace<float>> ilu;
+};
+}  // namespace
+
+EXPORT int64_t ref_ndata_f32(int nblocks, int blockw, int ndiag, int nsat, int ld) {
+    BlockDiagMatrix<float> m(nullptr, nblocks, blockw, ndiag, nsat, ld);
+    return m.m_ndata;
+}
+
+EXPORT int ref_default_ld_f32(int blockw) {
+    BlockDiagMatrix<float> m(nullptr, 1, blockw, 0, 0, 0);
+    return m.m_ld;
+}
+
+EXPORT void *ref_ilu_create_f32(float *data, int nblocks, int blockw, int ndiag, int nsat, int ld,
+                                int *ipiv, int *rowbycol, int *colbyrow, int *threw) {
+    auto *h = new RefILUf;
+    *threw = 0;
+    try {
+        h->view.reset(new BlockDiagMatrix<float>(data, nblocks, blockw, ndiag, nsat, ld));
+        h->ilu.reset(new ILU_inplace<float>(h->view.get()));
+    } catch (const std::exception &) {
+        *threw = 1;
+        delete h;
+        return nullptr;
+    }
+    const int n = nblocks * blockw;
+    for (int i = 0; i < n; ++i) {
+        if (ipiv) ipiv[i] = h->ilu->m_ipiv[i];
+        if (rowbycol) rowbycol[i] = h->ilu->m_rowbycol[i];
+        if (colbyrow) colbyrow[i] = h->ilu->m_colbyrow[i];
+    }
+    return h;
+}
+
+EXPORT int ref_ilu_solve_f32(void *handle, const float *b, float *x) {
+    return static_cast<RefILUf *>(handle)->ilu->solve(b, x);
+}
+
+EXPORT void ref_ilu_destroy_f32(void *handle) { delete static_cast<RefILUf *>(handle); }
+
+EXPORT void ref_dot_vec_f32(float *data, int nblocks, int blockw, int ndiag, int nsat, int ld,
+                            const float *vec, float *out) {
+    BlockDiagMatrix<float> m(data, nblocks, blockw, ndiag, nsat, ld);
+    m.dot_vec(vec, out);
+}
+
+EXPORT void ref_scale_diag_add_f32(float *dst, float *src, int nblocks, int blockw, int ndiag, int nsat,
+                                   int ld, float scale, float diag_add) {
+    BlockDiagMatrix<float> d(dst, nblocks, blockw, ndiag, nsat, ld);
+    BlockDiagMatrix<float> s(src, nblocks, blockw, ndiag, nsat, ld);
+    d.scale_diag_add(s, scale, diag_add);
+}

@@ -119,6 +119,48 @@ int main()
         bool threw = false;
         try { ILU_inplace<double> bad(&sing); } catch (const std::runtime_error &e) { threw = std::strcmp(e.what(), "ILU failed!") == 0; }
         CHECK(threw);
+
+        // --- MatrixBase source constructor (block_diag_ilu.hpp:124-159): entries inside the pattern are copied ---
+        {
+            struct Dense6 {
+                double a[6][6];
+                double operator()(int r, int c) const { return a[r][c]; }
+            } src;
+            for (int r = 0; r < 6; ++r)
+                for (int c = 0; c < 6; ++c) src.a[r][c] = 10 * (r + 1) + (c + 1);
+            BlockDiagMatrix<double> fromsrc(src, 3, 2, 1, 1);
+            CHECK(fromsrc.m_ld == 8 && fromsrc.m_nsat == 1);
+            for (int r = 0; r < 6; ++r)
+                for (int c = 0; c < 6; ++c)
+                    if (fromsrc.valid_index(r, c)) CHECK(fromsrc(r, c) == src.a[r][c]);
+            CHECK(fromsrc.bot(0, 0, 1) == src.a[5][1] && fromsrc.top(0, 0, 0) == src.a[0][4]);
+            BlockDiagMatrix<double> again(m4, 3, 2, 2, 0, 2);  // another BlockDiagMatrix as the source (:291-293)
+            for (int i = 0; i < m4.m_ndata; ++i) CHECK(again.m_data[i] == m4.m_data[i]);
+        }
+
+        // --- Real_t = float: the m2 case in single precision (the template parameter of hpp:104, 426) ---
+        {
+            BlockDiagMatrix<float> f2(nullptr, 3, 2, 1);
+            CHECK(f2.m_ld == 16);  // 64-byte rows: 16 floats (hpp:98)
+            const float blocks[3][2][2] = {{{5, 3}, {5, 8}}, {{8, 4}, {4, 4}}, {{6, 9}, {2, 7}}};
+            const float subv[2][2] = {{1, 2}, {3, 4}}, supv[2][2] = {{2, 3}, {4, 5}};
+            for (int bq = 0; bq < 3; ++bq)
+                for (int r = 0; r < 2; ++r)
+                    for (int c = 0; c < 2; ++c) f2.block(bq, r, c) = blocks[bq][r][c];
+            for (int bq = 0; bq < 2; ++bq)
+                for (int c = 0; c < 2; ++c) { f2.sub(0, bq, c) = subv[bq][c]; f2.sup(0, bq, c) = supv[bq][c]; }
+            float vf[6] = {3, 2, 6, 2, 5, 4}, of[6];
+            f2.dot_vec(vf, of);
+            CHECK(of[0] == 33.f && of[1] == 37.f && of[5] == 46.f);
+            ILU<float> iluf(f2);
+            const float bf[6] = {65, 202, 11, 65, 60, 121};
+            float xf[6];
+            CHECK(iluf.solve(bf, xf) == 0);
+            for (int i = 0; i < 6; ++i) CHECK(close(xf[i], xref[i], 2e-4));
+            CHECK(std::fabs(iluf.m_ilu_inplace.m_view->sub(0, 1, 0) - 3 / 8.f) < 1e-7f);
+            float bnf[6] = {65, 202, 11, std::numeric_limits<float>::quiet_NaN(), 60, 121};
+            CHECK(iluf.solve(bnf, xf) == 4);
+        }
     } catch (const std::runtime_error &e) {
         if (std::strstr(e.what(), "no CUDA device")) {
             std::printf("no CUDA device: %s\n", e.what());

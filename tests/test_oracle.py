@@ -211,3 +211,49 @@ def test_port_matches_reference_outputs(port, name):
     x, flag = port.solve(data, N, w, d, nsat, ld, rbc, cbr, b)
     assert flag == 0
     assert np.abs(x - z[name + "/x"]).max() <= tol * np.abs(z[name + "/x"]).max()
+
+
+# ---- Real_t = float: the float build of the reference header and its recorded outputs -----------------------------------
+GOLDEN_F32 = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_vectors_f32.npz")
+
+
+def _golden_f32_names():
+    z = np.load(GOLDEN_F32)
+    return sorted({k.split("/")[0] for k in z.files})
+
+
+def test_float_default_ld_and_ndata_match_the_reference():
+    """bdilu_default_ld_f32 / bdilu_ndata against BlockDiagMatrix<float>'s own arithmetic (hpp:98-102)."""
+    from block_diag_ilu_b200 import _lib
+    from oracle.loader import RefF32
+    try:
+        r = RefF32()
+    except (OSError, FileNotFoundError, AttributeError) as e:
+        pytest.skip("float reference shim unavailable: %s" % e)
+    L = _lib.lib()
+    for w in (1, 2, 3, 5, 8, 15, 16, 17, 31, 32, 33, 48, 64):
+        assert L.bdilu_default_ld_f32(w) == r.default_ld(w)
+        for (N, d, nsat) in ((1, 0, 0), (3, 1, 0), (7, 2, 2), (9, 3, 1)):
+            assert L.bdilu_ndata(N, w, d, nsat, L.bdilu_default_ld_f32(w)) == r.ndata(N, w, d, nsat, 0)
+
+
+@pytest.mark.parametrize("name", _golden_f32_names())
+def test_float_reference_reproduces_its_recorded_outputs(name):
+    """The committed float fixtures are what the reference computes here (bit for bit): they pin the GPU float tests."""
+    from oracle.loader import RefF32
+    try:
+        r = RefF32()
+    except (OSError, FileNotFoundError, AttributeError) as e:
+        pytest.skip("float reference shim unavailable: %s" % e)
+    z = np.load(GOLDEN_F32)
+    N, w, d, ld, nsat, seed = (int(v) for v in z[name + "/shape"])
+    data, b = synth.make_system(N, w, d, str(z[name + "/family"]), seed, ld=ld, nsat=nsat)
+    assert np.array_equal(data.astype(np.float32), z[name + "/data"]) and np.array_equal(b.astype(np.float32), z[name + "/b"])
+    fac = z[name + "/data"].copy()
+    assert np.array_equal(r.dot_vec(fac.copy(), N, w, d, nsat, ld, z[name + "/b"]), z[name + "/dot_vec"])
+    ipiv, rbc, cbr, info = r.factor(fac, N, w, d, nsat, ld)
+    assert info == 0 and np.array_equal(ipiv, z[name + "/ipiv"]) and np.array_equal(rbc, z[name + "/rowbycol"])
+    assert np.array_equal(cbr, z[name + "/colbyrow"]) and np.array_equal(fac, z[name + "/factored"])
+    x, flag = r.solve(fac, N, w, d, nsat, ld, rbc, cbr, z[name + "/b"])
+    assert flag == 0 and np.array_equal(x, z[name + "/x"])
+    r.release()
