@@ -26,6 +26,10 @@ constexpr int FACTOR_WARPS = 4;
 #define BDILU_FACTOR_PAIRED 1
 #endif
 constexpr bool PAIRED = BDILU_FACTOR_PAIRED != 0;  // blockw 32: two elimination steps per pivot-row publication
+#ifndef BDILU_FACTOR_OPTIMISTIC
+#define BDILU_FACTOR_OPTIMISTIC 1
+#endif
+constexpr bool OPTIMISTIC = BDILU_FACTOR_OPTIMISTIC != 0;  // blockw 32: diagonal pivots assumed and checked first (eliminate_diag32)
 constexpr bool SHFL_ROW = BDILU_FACTOR_SHFL_ROW != 0;  // blockw 32: pivot row by shuffle (1: 3.45 ms on cfg3) or mailbox (0: 3.2 ms)
 
 // argmax of v over the group with ties broken towards the lowest `pos`; returns the winning lane
@@ -104,6 +108,12 @@ __device__ __forceinline__ void sts128_if(bool p, unsigned saddr, double x, doub
 {
     asm volatile("{ .reg .pred p; setp.ne.u32 p, %3, 0; @p st.shared.v2.f64 [%0], {%1, %2}; }" ::"r"(saddr), "d"(x),
                  "d"(y), "r"((unsigned)p)
+                 : "memory");
+}
+
+__device__ __forceinline__ void sts64_if(bool p, unsigned saddr, double x)
+{
+    asm volatile("{ .reg .pred p; setp.ne.u32 p, %2, 0; @p st.shared.f64 [%0], %1; }" ::"r"(saddr), "d"(x), "r"((unsigned)p)
                  : "memory");
 }
 
@@ -275,6 +285,79 @@ __device__ __noinline__ void factor_block_slow(SrcView V, double *sysdata, doubl
     }
 }
 
+// ---- optimistic elimination (blockw 32) ------------------------------------------------------------------------------
+// The matrices this library exists for (I - gamma*J of a diffusion-reaction Jacobian, block_diag_ilu.hpp:288-290) are
+// diagonally dominant: partial pivoting then picks the diagonal at every step and ipiv is the identity.  This loop
+// ASSUMES that -- the pivot of step k is the row at position k, i.e. lane k, known at compile time -- and only CHECKS
+// it: idamax takes the first maximum, so the assumption holds exactly when no row below has a strictly larger modulus
+// in column k.  No reductions, no position bookkeeping, static pivot lanes; the arithmetic on every element is that of
+// the general loop (same publication in pairs, same Markstein quotients), so a block that passes the check comes out
+// bit-identical.  A block that fails it (a larger candidate, a NaN, a zero or out-of-range pivot) is reloaded and
+// redone by the general loop of factor_kernel, which then decides everything itself: the results never depend on
+// which path ran.  The check is voted every 8 steps so that blocks which do pivot leave early.
+// Returns true (warp-uniform) when the block is done: a[] holds row r of L\U, dgs[k] = (U[k][k], 1/U[k][k]).
+__device__ __forceinline__ bool eliminate_diag32(double (&a)[32], double (*urow)[34], double2 *dgs, int r)
+{
+    constexpr int WP = 32;
+    double2 *ub0 = reinterpret_cast<double2 *>(urow[0]);
+    double2 *ub1 = reinterpret_cast<double2 *>(urow[1]);
+    double *nx = &urow[0][WP];
+    const unsigned dgs_s = (unsigned)__cvta_generic_to_shared(dgs), nx_s = (unsigned)__cvta_generic_to_shared(nx);
+    bool viol = false;
+#pragma unroll
+    for (int k = 0; k < WP; k += 2) {
+        // ---- step k: lane k is the pivot row; the three numbers column k+1 needs ----
+        const double rcp0 = rcp_fast(a[k]);
+        sts128_if(r == k, dgs_s + 16u * k, a[k], rcp0);
+        sts64_if(r == k, nx_s, a[k + 1]);
+        __syncwarp();
+        const double2 d0 = dgs[k];
+        const double u0n = *nx;
+        const double piv0 = d0.x, rinv0 = d0.y;
+        const bool act0 = r > k;
+        viol |= act0 & !(fabs(a[k]) <= fabs(piv0));  // a larger candidate below, or a NaN on either side
+        double l0 = a[k] * rinv0;
+        l0 = fma(fma(-l0, piv0, a[k]), rinv0, l0);
+        a[k] = act0 ? l0 : a[k];
+        l0 = act0 ? l0 : 0.0;
+        a[k + 1] = fma(-l0, u0n, a[k + 1]);
+
+        // ---- step k+1: lane k+1 is the pivot row ----
+        const double rcp1 = rcp_fast(a[k + 1]);
+        sts128_if(r == k + 1, dgs_s + 16u * (k + 1), a[k + 1], rcp1);
+        {
+            // lanes k and k+1 in one predicated store sequence (see the general loop); buffer by arithmetic, no select
+            const unsigned rk = (unsigned)(r - k);
+            if (rk < 2u) {
+                double2 *dst = ub0 + rk * (WP / 2 + 1);  // urow[rk]
+#pragma unroll
+                for (int m = k / 2; m < WP / 2; ++m) dst[m] = make_double2(a[2 * m], a[2 * m + 1]);
+            }
+        }
+        __syncwarp();
+        const double2 hd = ub1[k / 2];
+        const double l0q = hd.x, piv1 = hd.y, rinv1 = dgs[k + 1].y;
+        const bool act1 = r > k + 1;
+        viol |= act1 & !(fabs(a[k + 1]) <= fabs(piv1));
+        double l1 = a[k + 1] * rinv1;
+        l1 = fma(fma(-l1, piv1, a[k + 1]), rinv1, l1);
+        a[k + 1] = act1 ? l1 : a[k + 1];
+        l1 = act1 ? l1 : 0.0;
+#pragma unroll
+        for (int m = k / 2 + 1; m < WP / 2; ++m) {
+            const double2 t0 = ub0[m], t1 = ub1[m];
+            const double u1x = fma(-l0q, t0.x, t1.x), u1y = fma(-l0q, t0.y, t1.y);
+            a[2 * m] = fma(-l1, u1x, fma(-l0, t0.x, a[2 * m]));
+            a[2 * m + 1] = fma(-l1, u1y, fma(-l0, t0.y, a[2 * m + 1]));
+        }
+        if ((k & 7) == 6 && k + 2 < WP && __any_sync(FULL, viol)) return false;
+    }
+    __syncwarp();
+    const double dg = dgs[r].x;  // a zero or out-of-range pivot: the general loop (info, true divisions) takes over
+    viol |= (dg == 0.0) || !rcp_fast_ok(dg);
+    return !__any_sync(FULL, viol);
+}
+
 // the source of a fused assembly (SCALED kernels only): J, its system stride, and M = scale*J + diag_add*I
 struct ScaledSrc {
     const double *src;
@@ -322,7 +405,18 @@ factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restric
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
     double2 *dgs = diag_s[wic][grp];
 
-    if constexpr (G == 32 && PAIRED && !SHFL_ROW) {
+    bool done = false;
+    if constexpr (G == 32 && PAIRED && !SHFL_ROW && OPTIMISTIC) {
+        done = eliminate_diag32(a, urow, dgs, r);  // pos = r, my_ipiv = r + 1 stand
+        if (!done) {
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < WP; ++c)
+                a[c] = (rowok && c < w) ? V.block_at(D.block(bi) + (int64_t)c * ld + r, c == r) : ((c == r) ? 1.0 : 0.0);
+        }
+    }
+    if (done) {
+    } else if constexpr (G == 32 && PAIRED && !SHFL_ROW) {
         // ---- two elimination steps per publication (blockw 32) --------------------------------------------------
         // A shared-memory store costs the register->MIO transfer of all 32 lanes whatever the number of active ones
         // (measured: STS.128 4.2 SM-cycles with 1 or 32 lanes, scratch/bw/mio_bench.cu), and that path bounds this
