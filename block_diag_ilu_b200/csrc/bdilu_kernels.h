@@ -33,11 +33,16 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
 
 extern int g_solve_path;  // test hook (7 = quad32; 8 = experimental systolic blockw-32 kernel first, quad32 behind it): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
                           // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
-                          // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it
+                          // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it,
+                          // 9 = prefetched narrow-block chain kernel (bdilu_solve_pf.cu) whenever the shape allows it
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
 bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                            cudaStream_t st, cudaError_t *err);
+// blockw <= 16 (bdilu_solve_pf.cu): one lane group per vector, every global load prefetched, the chain runs on shuffles
+bool try_launch_solve_pf(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
+                         const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags, cudaStream_t st,
+                         cudaError_t *err);
 bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                            cudaStream_t st, cudaError_t *err);

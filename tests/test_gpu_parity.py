@@ -96,7 +96,7 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8}
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9}
 
 
 @pytest.fixture(params=list(PATHS))
@@ -201,6 +201,23 @@ def test_config5_shape_subset(oracle):
 def test_satellites(oracle, nsat):
     run_case(oracle, 2, 9, 4, 1, "D", nsat=nsat)
     run_case(oracle, 2, 6, 8, 0, "P", nsat=nsat, ld=8)
+
+
+@pytest.mark.parametrize("path", ["auto", "chain"])
+@pytest.mark.parametrize("N,w,d,ld,nsat", [
+    (9, 4, 1, 4, 1), (12, 8, 2, 8, 2), (40, 8, 2, 8, 3), (33, 16, 1, 19, 2), (21, 5, 3, 8, 1), (30, 32, 2, 32, 2),
+    (17, 24, 1, 24, 3), (200, 32, 1, 32, 1), (16, 2, 4, 2, 4), (10, 48, 2, 48, 2),
+])
+def test_satellites_narrow_block_kernel(oracle, path, N, w, d, ld, nsat):
+    """Periodic couplings (block_diag_ilu.hpp:512-514, 528-530) on the automatic path -- the prefetched chain kernel for
+    blockw <= 32 with ndiag >= 1, the general chain kernel otherwise -- and on the general chain kernel alone."""
+    from block_diag_ilu_b200 import _lib
+    old = _lib.lib().bdilu_debug_force_chain_solve(PATHS[path])
+    try:
+        run_case(oracle, 3, N, w, d, "D", ld=ld, nrhs=2, nsat=nsat, seed0=41)
+        run_case(oracle, 2, N, w, d, "R", ld=ld, nrhs=1, nsat=nsat, seed0=43)
+    finally:
+        _lib.lib().bdilu_debug_force_chain_solve(old)
 
 
 @pytest.mark.parametrize("nrhs", [3, 5, 11])   # one vector per pass, ragged groups of 4 and of 8 vectors per pass
