@@ -30,6 +30,10 @@ constexpr bool PAIRED = BDILU_FACTOR_PAIRED != 0;  // blockw 32: two elimination
 #define BDILU_FACTOR_OPTIMISTIC 1
 #endif
 constexpr bool OPTIMISTIC = BDILU_FACTOR_OPTIMISTIC != 0;  // blockw 32: diagonal pivots assumed and checked first (eliminate_diag32)
+#ifndef BDILU_FACTOR_GRID2D
+#define BDILU_FACTOR_GRID2D 1
+#endif
+constexpr bool GRID2D = BDILU_FACTOR_GRID2D != 0;  // blockw == ld == 32: the optimistic path on a 16 x 2 lane grid (eliminate_diag32_grid)
 constexpr bool SHFL_ROW = BDILU_FACTOR_SHFL_ROW != 0;  // blockw 32: pivot row by shuffle (1: 3.45 ms on cfg3) or mailbox (0: 3.2 ms)
 
 // argmax of v over the group with ties broken towards the lowest `pos`; returns the winning lane
@@ -152,7 +156,7 @@ struct SrcView {
 
 // Stores what one lane owns after the elimination: its row of L\U at row `pos`, the permutation
 // vectors, the scaled sub/bot entries of column r, and the block's info.
-template <int WP>
+template <int WP, bool ROWS = true>
 __device__ __forceinline__ void store_block(const double (&a)[WP], const RowState &S, const SrcView &V, double *sysdata,
                                             double *blk, const Dims &D, int w, int ld, int sys, int bi, int r,
                                             int *__restrict__ ipiv, int *__restrict__ rowbycol,
@@ -167,9 +171,11 @@ __device__ __forceinline__ void store_block(const double (&a)[WP], const RowStat
 #pragma unroll
     for (int di = 0; di < PF; ++di)
         sv[di] = (di < nsub) ? V.at(D.off_sub + D.diag_chunk(di, bi) + r) : 0.0;
+    if (ROWS) {
 #pragma unroll
-    for (int c = 0; c < WP; ++c)
-        if (c < w) blk[(int64_t)c * ld + S.pos] = a[c];
+        for (int c = 0; c < WP; ++c)
+            if (c < w) blk[(int64_t)c * ld + S.pos] = a[c];
+    }
     const int64_t ib = ((int64_t)sys * D.nblocks + bi) * w;
     ipiv[ib + r] = S.ipiv;
     rowbycol[ib + S.pos] = r;
@@ -358,6 +364,71 @@ __device__ __forceinline__ bool eliminate_diag32(double (&a)[32], double (*urow)
     return !__any_sync(FULL, viol);
 }
 
+// The same optimistic elimination on a 2-D lane grid (blockw == ld == 32): lane = i + 16 j holds rows {i, i+16} and
+// the columns of parity j, t[a][b] = A[i + 16a][j + 2b].  With one lane per row every lane reads every element of every
+// pivot row (the shared-memory pipe bounds that kernel: l1tex lsu wavefronts 69 %, profiles/r02_ncu_full_summary.md);
+// here a lane reads only its half of the pivot row and uses each element for two rows, and the two pivot-row lanes
+// publish 8 + 8 doubles instead of one lane publishing 32.  The multipliers of column k are formed by the 16 lanes that
+// hold it and handed to their row partners by shuffle.  The 2-D layout sank an earlier attempt on the GENERAL
+// elimination (two-row pivot bookkeeping, scratch/factor32x2_experiment.patch); with static diagonal pivots there is no
+// bookkeeping left.  Element for element the operations are those of eliminate_diag32 without its pairing (each update
+// a -= l*u is one fma with the finished pivot-row value), hence those of the general loop: bit-identical results.
+__device__ __forceinline__ bool eliminate_diag32_grid(double (&t)[2][16], double *mb, double2 *dgs, int lane)
+{
+    const int i = lane & 15, j = lane >> 4;
+    bool viol = false;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+        const int pi = k & 15, ak = k >> 4, pj = k & 1, bk = k >> 1;
+        const int b0 = (pj == 0) ? bk : bk + 1;  // first column index (of either half) a reader may need
+        const double x = t[ak][bk];              // the pivot, in lane (pi, pj)
+        const double rc = rcp_fast(x);
+        double *buf = mb + (k & 1) * 32;         // double-buffered by step parity: one barrier per step is enough
+        if (i == pi) {
+            double2 *dst = reinterpret_cast<double2 *>(buf + j * 16);
+#pragma unroll
+            for (int m = b0 / 2; m < 8; ++m) dst[m] = make_double2(t[ak][2 * m], t[ak][2 * m + 1]);
+            if (j == pj) dgs[k] = make_double2(x, rc);
+        }
+        __syncwarp();
+        const double2 d = dgs[k];
+        const double piv = d.x, rinv = d.y;
+        const bool own = (j == pj);
+        double l[2] = {0.0, 0.0};
+#pragma unroll
+        for (int a = (k >= 15 ? 1 : 0); a < 2; ++a) {
+            const double xa = t[a][bk];
+            const bool act = (i + 16 * a) > k;
+            viol |= own & act & !(fabs(xa) <= fabs(piv));  // a larger candidate below, or a NaN on either side
+            double q = xa * rinv;
+            q = fma(fma(-q, piv, xa), rinv, q);
+            t[a][bk] = (own & act) ? q : xa;
+            q = group_bcast<32>(q, i | (pj << 4));  // from the lane of my row pair that holds column k
+            l[a] = act ? q : 0.0;
+        }
+        const double2 *src = reinterpret_cast<const double2 *>(buf + j * 16);
+#pragma unroll
+        for (int m = b0 / 2; m < 8; ++m) {
+            const double2 u = src[m];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int b = 2 * m + e;
+                if (b >= b0) {
+                    double ub = e ? u.y : u.x;
+                    if (pj == 0 && b == bk) ub = (j == 1) ? ub : 0.0;  // column k itself in the even half: multipliers
+#pragma unroll
+                    for (int a = (k >= 15 ? 1 : 0); a < 2; ++a) t[a][b] = fma(-l[a], ub, t[a][b]);
+                }
+            }
+        }
+        if ((k & 7) == 7 && k + 1 < 32 && __any_sync(FULL, viol)) return false;
+    }
+    __syncwarp();
+    const double dg = dgs[lane].x;  // a zero or out-of-range pivot: the general loop (info, true divisions) takes over
+    viol |= (dg == 0.0) || !rcp_fast_ok(dg);
+    return !__any_sync(FULL, viol);
+}
+
 // the source of a fused assembly (SCALED kernels only): J, its system stride, and M = scale*J + diag_add*I
 struct ScaledSrc {
     const double *src;
@@ -392,21 +463,45 @@ factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restric
     V.sys = SCALED ? SS.src + (int64_t)sys * SS.sys_stride : sysdata;
     V.scale = SS.scale; V.diag_add = SS.diag_add; V.scaled = SCALED;
 
+    double (*urow)[WP + 2] = urow_s[wic][grp];
+    double2 *dgs = diag_s[wic][grp];
+    double a[WP];
+    if constexpr (G == 32 && EXACT && OPTIMISTIC && GRID2D) {
+        // optimistic elimination on the 2-D lane grid; on success everything is stored from here
+        const int gi = lane & 15, gj = lane >> 4;
+        double t[2][16];
+#pragma unroll
+        for (int b = 0; b < 16; ++b)
+#pragma unroll
+            for (int aa = 0; aa < 2; ++aa)
+                t[aa][b] = V.block_at(D.block(bi) + (int64_t)(gj + 2 * b) * WP + gi + 16 * aa, gj + 2 * b == gi + 16 * aa);
+        if (eliminate_diag32_grid(t, &urow[0][0], dgs, lane)) {
+            if (live) {
+#pragma unroll
+                for (int b = 0; b < 16; ++b)
+#pragma unroll
+                    for (int aa = 0; aa < 2; ++aa) blk[(int64_t)(gj + 2 * b) * WP + gi + 16 * aa] = t[aa][b];
+                const double2 dd = dgs[r];
+                RowState S;
+                S.pos = r; S.ipiv = r + 1; S.info = 0; S.diag = dd.x; S.rinv = dd.y; S.fast = true;
+                store_block<WP, false>(a, S, V, sysdata, blk, D, w, ld, sys, bi, r, ipiv, rowbycol, colbyrow, info);
+            }
+            return;
+        }
+        __syncwarp();
+    }
     // row r of the block; rows/columns beyond w are padded with the identity (they pivot on themselves
     // in the trailing steps k >= w and never disturb the real rows)
-    double a[WP];
 #pragma unroll
     for (int c = 0; c < WP; ++c)
         a[c] = (rowok && c < w) ? V.block_at(D.block(bi) + (int64_t)c * ld + r, c == r) : ((c == r) ? 1.0 : 0.0);
 
-    double (*urow)[WP + 2] = urow_s[wic][grp];
     int pos = r;          // current position of my row in the swapped ordering
     bool active = true;   // not yet chosen as a pivot row (padded rows take part: see above)
     int my_ipiv = r + 1;  // lane k keeps ipiv[k]
-    double2 *dgs = diag_s[wic][grp];
 
     bool done = false;
-    if constexpr (G == 32 && PAIRED && !SHFL_ROW && OPTIMISTIC) {
+    if constexpr (G == 32 && PAIRED && !SHFL_ROW && OPTIMISTIC && !(EXACT && GRID2D)) {
         done = eliminate_diag32(a, urow, dgs, r);  // pos = r, my_ipiv = r + 1 stand
         if (!done) {
             __syncwarp();
