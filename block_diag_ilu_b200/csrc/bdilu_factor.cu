@@ -364,6 +364,45 @@ __device__ __forceinline__ bool eliminate_diag32(double (&a)[32], double (*urow)
     return !__any_sync(FULL, viol);
 }
 
+// The optimistic elimination for narrower blocks (G = 2..16 lanes per block, several blocks per warp): lane k of each
+// group is the pivot row of step k, one publication per step through the group's mailbox.  Same checks, same
+// arithmetic as the general loop; the vote is over the whole warp, so one group that has to pivot sends its
+// neighbours through the general loop as well (results do not depend on the path).
+template <int WP>
+__device__ __forceinline__ bool eliminate_diag_small(double (&a)[WP], double (*urow)[WP + 2], double2 *dgs, int r)
+{
+    bool viol = false;
+#pragma unroll
+    for (int k = 0; k < WP; ++k) {
+        const double rc = rcp_fast(a[k]);
+        double2 *ub = reinterpret_cast<double2 *>(urow[k & 1]);
+        if (r == k) {
+#pragma unroll
+            for (int m = (k + 1) / 2; m < WP / 2; ++m) ub[m] = make_double2(a[2 * m], a[2 * m + 1]);
+            dgs[k] = make_double2(a[k], rc);
+        }
+        __syncwarp();
+        const double2 d = dgs[k];
+        const double piv = d.x, rinv = d.y;
+        const bool act = r > k;
+        viol |= act & !(fabs(a[k]) <= fabs(piv));
+        double l = a[k] * rinv;
+        l = fma(fma(-l, piv, a[k]), rinv, l);
+        a[k] = act ? l : a[k];
+        l = act ? l : 0.0;
+#pragma unroll
+        for (int m = (k + 1) / 2; m < WP / 2; ++m) {
+            const double2 u = ub[m];
+            if (2 * m > k) a[2 * m] = fma(-l, u.x, a[2 * m]);
+            a[2 * m + 1] = fma(-l, u.y, a[2 * m + 1]);
+        }
+    }
+    __syncwarp();
+    const double dg = dgs[r].x;
+    viol |= (dg == 0.0) || !rcp_fast_ok(dg);
+    return !__any_sync(FULL, viol);
+}
+
 // The same optimistic elimination on a 2-D lane grid (blockw == ld == 32): lane = i + 16 j holds rows {i, i+16} and
 // the columns of parity j, t[a][b] = A[i + 16a][j + 2b].  With one lane per row every lane reads every element of every
 // pivot row (the shared-memory pipe bounds that kernel: l1tex lsu wavefronts 69 %, profiles/r02_ncu_full_summary.md);
@@ -503,6 +542,15 @@ factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restric
     bool done = false;
     if constexpr (G == 32 && PAIRED && !SHFL_ROW && OPTIMISTIC && !(EXACT && GRID2D)) {
         done = eliminate_diag32(a, urow, dgs, r);  // pos = r, my_ipiv = r + 1 stand
+        if (!done) {
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < WP; ++c)
+                a[c] = (rowok && c < w) ? V.block_at(D.block(bi) + (int64_t)c * ld + r, c == r) : ((c == r) ? 1.0 : 0.0);
+        }
+    }
+    if constexpr (G < 32 && OPTIMISTIC) {
+        done = eliminate_diag_small<WP>(a, urow, dgs, r);
         if (!done) {
             __syncwarp();
 #pragma unroll
