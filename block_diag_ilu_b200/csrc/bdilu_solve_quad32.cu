@@ -53,7 +53,9 @@ __device__ unsigned long long g_prof[8];
 #define Q32_ADD(slot, a, b)
 #endif
 
-// Debug builds (-DBDILU_SPIN_GUARD): a wait that spins for too long prints where it is stuck and traps.
+// Production builds: no wait can hang unnoticed: the producer warps' waits are clock-bounded and act as the watchdog of the
+// consumers (see produce()); a protocol failure ends in a trap = cudaErrorLaunchFailure, reported as BDILU_ERR_CUDA.
+// Debug builds (-DBDILU_SPIN_GUARD): a wait that spins for too long also prints where it is stuck.
 #ifdef BDILU_SPIN_GUARD
 #define Q32_GUARD_DECL long long guard_n = 0
 #define Q32_GUARD(what, a, b2, c)                                                                          \
@@ -70,7 +72,7 @@ __device__ __forceinline__ void mbar_wait_guard(void *bar, unsigned parity, cons
 #else
 #define Q32_GUARD_DECL
 #define Q32_GUARD(what, a, b2, c)
-#define mbar_wait_guard(bar, parity, what, a, b2, c) mbar_wait(bar, parity)
+#define mbar_wait_guard(bar, parity, what, a, b2, c) mbar_wait_unbounded(bar, parity)
 #endif
 
 // byte layout of one stage = one group of G blocks (every piece 16-byte aligned since ld is even)
@@ -103,6 +105,7 @@ struct Ctx {
     unsigned char *stages;
     unsigned long long *full, *empty;
     unsigned long long *started;  // [RS]: block of that ring slot has published its first quad
+    unsigned long long *sweep_done;  // one arrival per consumer warp at the end of each sweep (the producers' watchdog)
     double *ring;          // [RS][32]
     int *flagw;            // [2]: nan_first, zero_last
 };
@@ -132,7 +135,7 @@ __device__ void produce(const Ctx &C, int p, int lane)
         Q32_T(p0);
         const int gseq = (FWD ? 0 : C.NG) + g;
         const int s = gseq % C.NS, use = gseq / C.NS;
-        if (use >= 1) mbar_wait_guard(&C.empty[s], (unsigned)(use - 1) & 1u, FWD ? "prod empty fwd" : "prod empty bwd", g, s, use);
+        if (use >= 1) mbar_wait_timed(&C.empty[s], (unsigned)(use - 1) & 1u);  // watchdog: see the header
         Q32_T(p1);
         const int nb = min(G, N - g * G);
         const int b_lo = FWD ? g * G : N - g * G - nb;
@@ -182,6 +185,10 @@ __device__ void produce(const Ctx &C, int p, int lane)
         Q32_ADD(6, p1, p2);
         (void)ld;
     }
+    // Watchdog.  The consumers' waits and polls are unbounded (their instruction stream is too tight for a counter), but
+    // none of them can hang unnoticed: a stuck consumer stops releasing stages, so a producer's wait above times out; and
+    // after the last group the first producer warp waits, bounded, for every consumer warp to finish the sweep.
+    if (p == 0) mbar_wait_timed(C.sweep_done, FWD ? 0u : 1u);
 }
 
 // ---- consumers: lane = row, warp j owns sweep orders j, j+QW, ... -------------------------------------------------
@@ -402,6 +409,8 @@ __device__ void consume(const Ctx &C, int j, int r, int &nan_first, int &zero_la
         Q32_ADD(4, t4, t5);
         Q32_ADD(7, 0, 1);
     }
+    __syncwarp();
+    if (r == 0) mbar_arrive(C.sweep_done);
 }
 
 template <int ND, int MODE, bool LD32>
@@ -435,7 +444,8 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
     C.empty = C.full + NS;
     off += (size_t)2 * NS * 8;
     C.started = C.empty + NS;
-    off += (size_t)RS * 8;
+    C.sweep_done = C.started + RS;
+    off += (size_t)(RS + 1) * 8;
     C.ring = reinterpret_cast<double *>(smem_raw + off);
     off += (size_t)RS * 32 * 8;
     C.flagw = reinterpret_cast<int *>(smem_raw + off);
@@ -446,6 +456,7 @@ solve_quad32_kernel(const double *__restrict__ data, int64_t sys_stride, Dims D,
             mbar_init(&C.empty[s], G);
         }
         for (int t = 0; t < RS; ++t) mbar_init(&C.started[t], 1);
+        mbar_init(C.sweep_done, QW);
         C.flagw[0] = 0x7fffffff;
         C.flagw[1] = -1;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -549,7 +560,7 @@ bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stri
 {
     using namespace quad;
     const GroupLayout GL = group_layout(D.ld, D.ndiag);
-    const size_t fixed = (size_t)RS * 32 * 8 + (size_t)RS * 8 + 64;
+    const size_t fixed = (size_t)RS * 32 * 8 + (size_t)(RS + 1) * 8 + 64;
     const size_t budget = 227 * 1024;
     int NS = (int)((budget - fixed) / (GL.bytes + 16));
     if (NS > 16) NS = 16;

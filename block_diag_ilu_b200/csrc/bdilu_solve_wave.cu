@@ -42,9 +42,11 @@ __device__ void consume(const Args &A, const Smem &S, int it0, int j, int r, int
         if (i >= NW) {
             for (int d = 0; d < ND; ++d) {
                 const int oi = i - NW + 1 + d;
-                if (oi < N)
-                    while (ld_volatile_s(&S.done[oi % NW]) < oi + 1) {
-                    }
+                if (oi < N) {
+                    unsigned spins = 0;
+                    while (ld_volatile_s(&S.done[oi % NW]) < oi + 1)
+                        if (++spins > SPIN_LIMIT) __trap();
+                }
             }
             st_volatile_s(&S.ring[((i + NW) % (2 * NW)) * 32 + r], __longlong_as_double((long long)SENT));
         }
@@ -109,7 +111,13 @@ __device__ void consume(const Args &A, const Smem &S, int it0, int j, int r, int
             const double lk = (rowok && (FWD ? r > k : r < k)) ? Ls[k * ld + r] : 0.0;
             if (need) poll();
             const bool apply_now = rowok && k == kapply;
-            while (__any_sync(FULL, apply_now && need != 0)) poll();
+            {
+                unsigned spins = 0;
+                while (__any_sync(FULL, apply_now && need != 0)) {
+                    if (++spins > SPIN_LIMIT) __trap();
+                    poll();
+                }
+            }
             if (apply_now) acc -= cacc;
             if (!FWD && r == k) {
                 // x = acc / U[k][k]: reciprocal + one Newton correction gives the correctly rounded

@@ -206,11 +206,13 @@ __device__ void consume32(const Args &A, const Smem &S, int s0, unsigned ph0, in
         // Warp-uniform wait until the lanes selected by `mine` hold real predecessor values in v[] (no lane ever
         // spins on its own, so the warp never splits); the first test uses the values loaded a step earlier.
         auto await_pred = [&](bool mine) {
+            unsigned spins = 0;
             for (;;) {
                 bool bad = false;
 #pragma unroll
                 for (int d = 0; d < ND; ++d) bad |= is_sent(v[d]);
                 if (!__any_sync(FULL, mine && bad)) break;
+                if (++spins > SPIN_LIMIT) __trap();  // bounded: traps instead of hanging
                 load_pred();
             }
         };

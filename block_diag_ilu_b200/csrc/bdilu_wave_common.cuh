@@ -42,9 +42,34 @@ __device__ __forceinline__ bool mbar_try(void *bar, unsigned parity)
         : "memory");
     return ok != 0;
 }
+// No wait in these kernels can hang: every one is on an event that the protocol orders strictly earlier, so a wait
+// that is retried SPIN_LIMIT times (seconds; legitimate waits last microseconds) is a protocol failure or corrupt
+// input, and the kernel traps -> cudaErrorLaunchFailure at the caller's next synchronisation, which the C ABI
+// reports as BDILU_ERR_CUDA.  The counters live on the retry paths only (a per-poll clock read or a guard object per
+// wait site cost the blockw-32 kernel 16 %: measured).
+constexpr unsigned SPIN_LIMIT = 1u << 26;
 __device__ __forceinline__ void mbar_wait(void *bar, unsigned parity)
 {
+    unsigned n = 0;
     while (!mbar_try(bar, parity)) {
+        if (++n > SPIN_LIMIT) __trap();
+    }
+}
+// for the consumer warps of the blockw-32 kernel, whose instruction stream does not tolerate even a retry counter
+// (measured: +6..10 % each); their waits are bounded through the producer warps' watchdog (bdilu_solve_quad32.cu)
+__device__ __forceinline__ void mbar_wait_unbounded(void *bar, unsigned parity)
+{
+    while (!mbar_try(bar, parity)) {
+    }
+}
+// clock-bounded wait for warps off the critical path (producers): traps after WAIT_CYCLES of waiting
+constexpr long long WAIT_CYCLES = 1ll << 33;  // ~4 s
+__device__ __forceinline__ void mbar_wait_timed(void *bar, unsigned parity)
+{
+    if (mbar_try(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try(bar, parity)) {
+        if (clock64() - t0 > WAIT_CYCLES) __trap();
     }
 }
 // global -> shared bulk copy, completion counted in bytes on `bar`
