@@ -13,6 +13,24 @@
 namespace bdilu {
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int sm_count()
+{
+    static std::atomic<int> cache[64];  // 0 = not asked yet
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        cudaGetLastError();
+        return 148;
+    }
+    int n = cache[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) {
+            cudaGetLastError();
+            n = 148;
+        }
+        cache[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
 }  // namespace bdilu
 
 using namespace bdilu;

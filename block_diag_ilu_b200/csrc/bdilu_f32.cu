@@ -592,7 +592,7 @@ int bdilu_scale_diag_add_f32(float *dst, const float *src, int64_t sys_stride, i
     const int64_t want = (D.ndata + 255) / 256;
     for (int s0 = 0; s0 < nsys; s0 += f32::MAX_GRID_YZ) {
         const int ns = nsys - s0 < f32::MAX_GRID_YZ ? nsys - s0 : f32::MAX_GRID_YZ;
-        dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), ns);
+        dim3 grid((unsigned)(want < sm_count() * 8 ? want : sm_count() * 8), ns);
         f32::scale_diag_add_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
             dst + (int64_t)s0 * sys_stride, src + (int64_t)s0 * sys_stride, sys_stride, D, scale, diag_add);
         count_launch(1);

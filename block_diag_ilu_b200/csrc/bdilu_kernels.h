@@ -8,6 +8,9 @@
 namespace bdilu {
 
 void count_launch(int n);
+// SMs of the current device (148 on a full B200), cached per device: grid sizes and the fill thresholds of the solve
+// dispatch are expressed in it
+int sm_count();
 void set_last_error(const char *msg);  // feeds bdilu_last_error() on the calling thread
 
 // argument checks / error channel of the C ABI, shared by the translation units that hold entry points

@@ -299,7 +299,7 @@ cudaError_t launch_scale_diag_add(double *dst, const double *src, int64_t dst_st
     const int64_t want = (D.ndata + 255) / 256;
     for (int s0 = 0; s0 < nsys; s0 += MAX_GRID_YZ) {
         const int ns = nsys - s0 < MAX_GRID_YZ ? nsys - s0 : MAX_GRID_YZ;
-        dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), ns);
+        dim3 grid((unsigned)(want < sm_count() * 8 ? want : sm_count() * 8), ns);
         scale_diag_add_kernel<<<grid, 256, 0, st>>>(dst + (int64_t)s0 * dst_stride, src + (int64_t)s0 * src_stride, dst_stride,
                                                     src_stride, D, scale, diag_add);
         count_launch(1);

@@ -230,7 +230,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
         if (D.nsat > 0) pf_first = true;
         else if (D.w <= 4) pf_first = !(groups_fit && V.nrhs >= 8) && total <= 20000;
         else if (!groups_fit || D.nblocks < 128) pf_first = V.nrhs < 8 || !groups_fit;
-        else pf_first = V.nrhs < 8 && total >= (D.w <= 8 ? 384 : 128);
+        else pf_first = V.nrhs < 8 && total >= (D.w <= 8 ? 384 : 128) * (int64_t)sm_count() / 148;
     }
     if (pf_first && try_launch_solve_pf(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr)) return werr;
     if (try_launch_solve_mrhs(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr)) return werr;

@@ -333,6 +333,7 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     using namespace mrhs;
     *err = cudaSuccess;
     const int w = D.w;
+    const int nsm = sm_count();
     if (g_solve_path != 0 && g_solve_path != 4 && g_solve_path != 6) return false;
     if (w > 64 || w < 4 || (w & 3) || (D.ld & 1) || D.ndiag > MAXD || D.nsat != 0 || D.nblocks < 1) return false;
     if (sys_stride & 1) return false;
@@ -346,14 +347,14 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     // each warp's instruction stream per block (the chain over the blocks is what bounds the run time).
     int Q = 4;
     if (fullw) {
-        while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 16 / Q - 1) / (16 / Q)) <= 2 * 148) Q *= 2;
+        while (Q < 16 && WP >= 4 * Q && (int64_t)nsys * ((V.nrhs + 16 / Q - 1) / (16 / Q)) <= 2 * nsm) Q *= 2;
     }
     const int64_t nvec = (int64_t)nsys * V.nrhs;
     const int64_t groups = (int64_t)nsys * ((V.nrhs + 32 / Q - 1) / (32 / Q));
     // The wavefront form (bdilu_solve_mrhs_wave.cu: one CTA per group, K warps on consecutive blocks) shortens the
     // chain's latency; it pays while the GPU is not full of groups.  With more groups than that the one-warp-per-group
     // form below has the better throughput (blocks staged once for up to 4 groups).
-    bool wave = fullw && groups <= 2 * 148;
+    bool wave = fullw && groups <= 2 * nsm;
     if (g_solve_path == 0) {
         // Measured on B200 (scratch/mrhs_time.py).  blockw 64 has no one-vector wavefront kernel to compete with
         // (cfg4: chain 44.9 ms, one warp per group 13.5 ms, wavefront form 7.7 ms).  At blockw 32 a quad32 CTA finishes
@@ -366,7 +367,7 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
         if (w > 32) use = true;  // even one vector: 5.9 ms in a wavefront group against ~40 ms on the chain kernel
         else if (w == 32) {
             wave = false;
-            use = V.nrhs >= 8 && nvec > 14 * 148;
+            use = V.nrhs >= 8 && nvec > 14 * nsm;
         } else if (D.nblocks >= 128 && fullw) {
             // blockw 8 / 16, chains long enough to amortise the pipeline fill.  The group kernels also beat the
             // one-vector kernels when every group holds a single live vector (ms, one vector per system):
@@ -374,10 +375,10 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
             //                          600: 3.60 wavefront, 3.27 one warp per group / 6.32;  1200: 6.18, 3.65 / 6.83
             //   blockw 8, N = 512:     64: 0.53 / 0.71;  512: 0.74 / 2.38;  1024: 1.37, 1.49 / 2.45;
             //                          1536: 2.03, 1.58 / 2.41;  2048: 2.58, 1.77 / 2.39;  4096: 4.87, 3.30 / 2.41
-            wave = groups <= (w == 8 ? 1024 : 2 * 148);
-            use = wave || groups <= (w == 8 ? 2560 : 2400) || (V.nrhs >= 8 && nvec > 8 * 148);
+            wave = groups <= (w == 8 ? 7 * nsm : 2 * nsm);
+            use = wave || groups <= (w == 8 ? 17 * nsm : 16 * nsm) || (V.nrhs >= 8 && nvec > 8 * nsm);
         } else {
-            use = V.nrhs >= 8 && nvec > 8 * 148;
+            use = V.nrhs >= 8 && nvec > 8 * nsm;
         }
         if (!use) return false;
     }
@@ -388,7 +389,7 @@ bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, con
     const int R = 32 / Q;
     const int gps = (V.nrhs + R - 1) / R;
     const int64_t total_groups = (int64_t)nsys * gps;
-    int nwc = (int)((total_groups + 147) / 148);
+    int nwc = (int)((total_groups + nsm - 1) / nsm);
     if (nwc > MAXWARPS) nwc = MAXWARPS;
     if (nwc > gps) nwc = gps;
     if (nwc < 1) nwc = 1;

@@ -244,7 +244,7 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
     const int64_t nvec = (int64_t)nsys * V.nrhs;
     if (w > 32 || w < 4 || (w & 3) || (D.ld & 1) || D.ndiag < 1 || D.ndiag > MAXD || D.nsat != 0) return false;
     if (D.nblocks < 4 * NW) return false;                       // short chains: nothing to pipeline
-    if (nvec > 8 * 148 && w < 32) return false;                 // wide batches of small systems: chain kernel
+    if (nvec > 8 * sm_count() && w < 32) return false;                 // wide batches of small systems: chain kernel
     if ((sys_stride & 1) || (V.rhs_stride & 1) || (V.sys_stride & 1)) return false;
     if ((reinterpret_cast<uintptr_t>(data) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(rowbycol) |
          reinterpret_cast<uintptr_t>(colbyrow)) & 15)
