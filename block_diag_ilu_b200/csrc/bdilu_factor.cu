@@ -33,6 +33,11 @@ constexpr bool OPTIMISTIC = BDILU_FACTOR_OPTIMISTIC != 0;  // blockw 32: diagona
 #ifndef BDILU_FACTOR_GRID2D
 #define BDILU_FACTOR_GRID2D 1
 #endif
+#ifndef BDILU_FACTOR_GRID_PAIRED
+#define BDILU_FACTOR_GRID_PAIRED 0
+#endif
+constexpr bool GRID_PAIRED = BDILU_FACTOR_GRID_PAIRED != 0;  // ... with two steps per publication (eliminate_diag32_grid2): measured
+                                                             // 2.55 ms against 2.41 ms unpaired on cfg3, so off
 constexpr bool GRID2D = BDILU_FACTOR_GRID2D != 0;  // blockw == ld == 32: the optimistic path on a 16 x 2 lane grid (eliminate_diag32_grid)
 constexpr bool SHFL_ROW = BDILU_FACTOR_SHFL_ROW != 0;  // blockw 32: pivot row by shuffle (1: 3.45 ms on cfg3) or mailbox (0: 3.2 ms)
 
@@ -468,11 +473,111 @@ __device__ __forceinline__ bool eliminate_diag32_grid(double (&t)[2][16], double
     return !__any_sync(FULL, viol);
 }
 
+// The grid elimination with TWO steps per publication (as the one-lane-per-row loop does, and for the same reason: a
+// shared-memory store costs the register -> MIO transfer of all 32 lanes whatever the number of active ones, and that
+// queue is the busiest unit of this kernel: sm__mio_pq_write 64 % with one publication per step).  Rows k and k+1
+// (k even) go out in ONE store sequence with four lanes active; row k+1 is published as it stands, i.e. without step
+// k's update in the columns beyond k+1, and every lane redoes that update itself: u1 = r1 - l0(k+1) * u0, the same fma
+// the owner would have done.  Results are bit-identical to the unpaired loops.
+// MEASURED AND NOT USED (-DBDILU_FACTOR_GRID_PAIRED=1 to build it): stores 168 -> 128 per block, but 16 % more DFMAs and
+// 8 % more instructions; cfg3 factor 2.55 ms against 2.41 ms for eliminate_diag32_grid.
+__device__ __forceinline__ bool eliminate_diag32_grid2(double (&t)[2][16], double *mb, double2 *dgs, int lane)
+{
+    const int i = lane & 15, j = lane >> 4;
+    bool viol = false;
+#pragma unroll
+    for (int k = 0; k < 32; k += 2) {
+        const int pi0 = k & 15, a0 = k >> 4, bk = k >> 1, pi1 = pi0 + 1;  // rows k, k+1 sit in slot a0 of lanes pi0, pi1
+        const int as = (k >= 15) ? 1 : 0;                                   // first slot with rows still active
+        // ---- step k: pivot in lane (pi0, 0); column k+1 needs (pivot, 1/pivot) and the pivot row's entry in column k+1
+        {
+            const double x0 = t[a0][bk];
+            const double rc0 = rcp_fast(x0);
+            if (i == pi0) {
+                if (j == 0) dgs[k] = make_double2(x0, rc0);
+                else mb[64] = x0;  // (pi0, 1): row k, column k+1
+            }
+        }
+        __syncwarp();
+        double l0[2] = {0.0, 0.0}, l1[2] = {0.0, 0.0};
+        {
+            const double2 d0 = dgs[k];
+            const double piv0 = d0.x, rinv0 = d0.y;
+            const double u0n = (j == 1) ? mb[64] : 0.0;
+#pragma unroll
+            for (int a = as; a < 2; ++a) {
+                const double xa = t[a][bk];
+                const bool act = (i + 16 * a) > k;
+                viol |= (j == 0) & act & !(fabs(xa) <= fabs(piv0));
+                double q = xa * rinv0;
+                q = fma(fma(-q, piv0, xa), rinv0, q);
+                t[a][bk] = ((j == 0) & act) ? q : xa;
+                q = group_bcast<32>(q, i);  // from lane (i, 0), which holds column k of my rows
+                l0[a] = act ? q : 0.0;
+                t[a][bk] = fma(-l0[a], u0n, t[a][bk]);  // column k+1 in the odd half (u0n = 0 in the even half)
+            }
+        }
+        // ---- step k+1: pivot in lane (pi1, 1); rows k and k+1 are published together
+        {
+            const double x1 = t[a0][bk];
+            const double rc1 = rcp_fast(x1);
+            const unsigned rk = (unsigned)(i - pi0);
+            if (rk < 2u) {
+                double2 *dst = reinterpret_cast<double2 *>(mb + rk * 32 + j * 16);
+#pragma unroll
+                for (int m = (bk + 1) / 2; m < 8; ++m) dst[m] = make_double2(t[a0][2 * m], t[a0][2 * m + 1]);
+                if (rk == 1u) {
+                    if (j == 1) dgs[k + 1] = make_double2(x1, rc1);
+                    else mb[65] = x1;  // (pi1, 0): the multiplier of row k+1 against row k
+                }
+            }
+        }
+        __syncwarp();
+        {
+            const double2 d1 = dgs[k + 1];
+            const double piv1 = d1.x, rinv1 = d1.y, l0q = mb[65];
+#pragma unroll
+            for (int a = as; a < 2; ++a) {
+                const double xa = t[a][bk];
+                const bool act = (i + 16 * a) > k + 1;
+                viol |= (j == 1) & act & !(fabs(xa) <= fabs(piv1));
+                double q = xa * rinv1;
+                q = fma(fma(-q, piv1, xa), rinv1, q);
+                t[a][bk] = ((j == 1) & act) ? q : xa;
+                q = group_bcast<32>(q, i | 16);  // from lane (i, 1), which holds column k+1 of my rows
+                l1[a] = act ? q : 0.0;
+            }
+            const double2 *U0 = reinterpret_cast<const double2 *>(mb + j * 16);
+            const double2 *R1 = reinterpret_cast<const double2 *>(mb + 32 + j * 16);
+#pragma unroll
+            for (int m = (bk + 1) / 2; m < 8; ++m) {
+                const double2 u0 = U0[m], r1 = R1[m];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int b = 2 * m + e;
+                    if (b > bk) {
+                        const double u0v = e ? u0.y : u0.x, r1v = e ? r1.y : r1.x;
+                        const double u1 = fma(-l0q, u0v, r1v);
+#pragma unroll
+                        for (int a = as; a < 2; ++a) t[a][b] = fma(-l1[a], u1, fma(-l0[a], u0v, t[a][b]));
+                    }
+                }
+            }
+        }
+        if ((k & 7) == 6 && k + 2 < 32 && __any_sync(FULL, viol)) return false;
+    }
+    __syncwarp();
+    const double dg = dgs[lane].x;
+    viol |= (dg == 0.0) || !rcp_fast_ok(dg);
+    return !__any_sync(FULL, viol);
+}
+
 // the source of a fused assembly (SCALED kernels only): J, its system stride, and M = scale*J + diag_add*I
 struct ScaledSrc {
     const double *src;
     int64_t sys_stride;
     double scale, diag_add;
+    int ahead;  // blockw == ld == 32: L2 look-ahead distance in blocks (0 = off)
 };
 
 template <int WP, bool EXACT, bool SCALED>
@@ -505,6 +610,18 @@ factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restric
     double (*urow)[WP + 2] = urow_s[wic][grp];
     double2 *dgs = diag_s[wic][grp];
     double a[WP];
+    if constexpr (G == 32 && EXACT) {
+        // L2 prefetch of the block that the warp taking this one's place will load (a CTA lives for one block per warp and
+        // starts with a cold read of 8 KB): about one generation of resident warps ahead
+        const int64_t ahead = gb + SS.ahead;
+        if (SS.ahead > 0 && ahead < total) {
+            const int psys = (int)(ahead / D.nblocks), pbi = (int)(ahead % D.nblocks);
+            const char *pb = reinterpret_cast<const char *>((SCALED ? SS.src + (int64_t)psys * SS.sys_stride
+                                                                    : data + (int64_t)psys * sys_stride) + D.block(pbi));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + 128 * lane));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + 128 * (lane + 32)));
+        }
+    }
     if constexpr (G == 32 && EXACT && OPTIMISTIC && GRID2D) {
         // optimistic elimination on the 2-D lane grid; on success everything is stored from here
         const int gi = lane & 15, gj = lane >> 4;
@@ -514,7 +631,7 @@ factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restric
 #pragma unroll
             for (int aa = 0; aa < 2; ++aa)
                 t[aa][b] = V.block_at(D.block(bi) + (int64_t)(gj + 2 * b) * WP + gi + 16 * aa, gj + 2 * b == gi + 16 * aa);
-        if (eliminate_diag32_grid(t, &urow[0][0], dgs, lane)) {
+        if (GRID_PAIRED ? eliminate_diag32_grid2(t, &urow[0][0], dgs, lane) : eliminate_diag32_grid(t, &urow[0][0], dgs, lane)) {
             if (live) {
 #pragma unroll
                 for (int b = 0; b < 16; ++b)
@@ -835,9 +952,14 @@ factor_wide_kernel(double *__restrict__ data, int64_t sys_stride, int nsys, Dims
 }
 
 // src == nullptr: in place.  Otherwise the fused assembly data = LU(scale*src + diag_add*I) (src may equal data).
+#ifndef BDILU_FACTOR_AHEAD
+#define BDILU_FACTOR_AHEAD 16  // look-ahead in units of (SMs x warps per CTA): 4 CTAs x 4 warps resident per SM
+#endif
 static cudaError_t launch_factor_any(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv, int *rowbycol,
-                                     int *colbyrow, int *info, const ScaledSrc &SS, cudaStream_t st)
+                                     int *colbyrow, int *info, const ScaledSrc &SS0, cudaStream_t st)
 {
+    ScaledSrc SS = SS0;
+    SS.ahead = (D.w == 32 && D.ld == 32) ? sm_count() * BDILU_FACTOR_AHEAD : 0;
     const int64_t total = (int64_t)nsys * D.nblocks;
     if (total == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(info, 0, sizeof(int) * (size_t)nsys, st);
@@ -874,7 +996,7 @@ static cudaError_t launch_factor_any(double *data, int64_t sys_stride, int nsys,
 cudaError_t launch_factor(double *data, int64_t sys_stride, int nsys, const Dims &D, int *ipiv,
                           int *rowbycol, int *colbyrow, int *info, cudaStream_t st)
 {
-    const ScaledSrc none = {nullptr, 0, 1.0, 0.0};
+    const ScaledSrc none = {nullptr, 0, 1.0, 0.0, 0};
     return launch_factor_any(data, sys_stride, nsys, D, ipiv, rowbycol, colbyrow, info, none, st);
 }
 
@@ -882,7 +1004,7 @@ cudaError_t launch_factor_scaled(double *dst, int64_t dst_stride, const double *
                                  const Dims &D, double scale, double diag_add, int *ipiv, int *rowbycol, int *colbyrow,
                                  int *info, cudaStream_t st)
 {
-    const ScaledSrc SS = {src, src_stride, scale, diag_add};
+    const ScaledSrc SS = {src, src_stride, scale, diag_add, 0};
     return launch_factor_any(dst, dst_stride, nsys, D, ipiv, rowbycol, colbyrow, info, SS, st);
 }
 
