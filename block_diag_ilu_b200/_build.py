@@ -5,7 +5,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libbdilu_b200.so")
-SOURCES = ["bdilu_factor.cu", "bdilu_solve.cu", "bdilu_solve_pf.cu", "bdilu_solve_skew.cu", "bdilu_solve_wave.cu", "bdilu_solve_wave32.cu", "bdilu_solve_quad32.cu", "bdilu_solve_mrhs.cu", "bdilu_solve_mrhs_wave.cu", "bdilu_matvec.cu", "bdilu_f32.cu", "bdilu_capi.cu", "bdilu_host.cu"]
+SOURCES = ["bdilu_factor.cu", "bdilu_solve.cu", "bdilu_solve_pf.cu", "bdilu_solve_skew.cu", "bdilu_solve_wave.cu", "bdilu_solve_wave32.cu", "bdilu_solve_quad32.cu", "bdilu_solve_half32.cu", "bdilu_solve_mrhs.cu", "bdilu_solve_mrhs_wave.cu", "bdilu_matvec.cu", "bdilu_f32.cu", "bdilu_capi.cu", "bdilu_host.cu"]
 HEADERS = ["bdilu_common.cuh", "bdilu_kernels.h", "bdilu_wave_common.cuh", "bdilu_mrhs_common.cuh", os.path.join("..", "..", "include", "bdilu.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--cudart", "shared"]

@@ -37,7 +37,8 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
 extern int g_solve_path;  // test hook (7 = quad32; 8 = experimental systolic blockw-32 kernel first, quad32 behind it): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
                           // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
                           // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it,
-                          // 9 = prefetched narrow-block chain kernel (bdilu_solve_pf.cu) whenever the shape allows it
+                          // 9 = prefetched narrow-block chain kernel (bdilu_solve_pf.cu) whenever the shape allows it,
+                          // 10 = two-SM blockw-32 kernel (bdilu_solve_half32.cu) first, quad32 behind it, whatever the batch size
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
 bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                            const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
@@ -59,6 +60,14 @@ cudaError_t launch_solve_wave32(unsigned nvec, size_t smem, int NS, const double
 bool try_launch_solve_quad32(unsigned nvec, const double *data, int64_t sys_stride, const Dims &D, const int *rowbycol,
                              const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags,
                              cudaStream_t st, cudaError_t *err, const int *status = nullptr);
+
+// blockw == 32 on two SMs per chain (bdilu_solve_half32.cu): rows 0..15 and 16..31 of every block on the two CTAs of a
+// cluster, the dependency between them one-directional per sweep.  Solves the vectors whose systems never pivoted across the
+// middle of a block and marks the others in `status` (int per vector) for quad32; `scratch`: nvec * half32_scratch_ints() ints.
+int half32_scratch_ints();
+bool try_launch_solve_half32(unsigned nvec, const double *data, int64_t sys_stride, int nsys, const Dims &D,
+                             const int *rowbycol, const int *colbyrow, const double *b, double *x, const VecLayout &V,
+                             int *flags, int *status, int *scratch, cudaStream_t st, cudaError_t *err);
 
 // blockw == 32 systolic solve (bdilu_solve_skew.cu; experimental, opt-in): lane = block, consecutive blocks one row
 // apart.  Handles the vectors whose permutations are the identity (status == 0 after the permutation scan) and hands

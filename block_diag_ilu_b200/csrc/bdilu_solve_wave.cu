@@ -284,7 +284,34 @@ bool try_launch_solve_wave(const double *data, int64_t sys_stride, int nsys, con
             (void)cudaGetLastError();
         }
     }
-    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5 || g_solve_path == 7 || g_solve_path == 8) &&
+#ifndef BDILU_HALF32_AUTO
+#define BDILU_HALF32_AUTO 0
+#endif
+    if (w == 32 && (g_solve_path == 10 || (g_solve_path == 0 && BDILU_HALF32_AUTO && 2 * nvec <= sm_count()))) {
+        // two SMs per chain while the batch leaves half of the GPU idle (cfg3: 64 chains on 148 SMs); the vectors of
+        // systems that pivoted across the middle of a block come back through `status` and run on quad32 behind it
+        int *scr = nullptr;
+        const size_t ints = (size_t)nvec * (1 + (size_t)half32_scratch_ints());
+        if (cudaMallocAsync(reinterpret_cast<void **>(&scr), sizeof(int) * ints, st) == cudaSuccess) {
+            int *status = scr, *scratch = scr + nvec;
+            if (try_launch_solve_half32((unsigned)nvec, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, status,
+                                        scratch, st, err)) {
+                if (*err == cudaSuccess &&
+                    try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err, status)) {
+                    count_launch(3);
+                    cudaFreeAsync(scr, st);
+                    return true;
+                }
+                cudaFreeAsync(scr, st);
+                if (*err != cudaSuccess) return true;
+            } else {
+                cudaFreeAsync(scr, st);
+            }
+        } else {
+            (void)cudaGetLastError();
+        }
+    }
+    if (w == 32 && (g_solve_path == 0 || g_solve_path == 5 || g_solve_path == 7 || g_solve_path == 8 || g_solve_path == 10) &&
         try_launch_solve_quad32((unsigned)nvec, data, sys_stride, D, rowbycol, colbyrow, b, x, V, flags, st, err)) {
         count_launch(1);
         return true;

@@ -10,6 +10,7 @@ python_prototype/demo.py:35-60).  Two families:
                   ("non-degenerate": a rounding difference between two correct eliminations must not flip a pivot)
   "R"  permuted : a family-D block with its rows shuffled: every block pivots, and partial pivoting undoes the
                   shuffle, so the chain is as well conditioned as D's (pivot parity at the full 1e-12 bar)
+  "H"  halves   : as R with the shuffle confined to the upper and the lower half of each block
 
 Layout follows block_diag_ilu.hpp:99-102 (blocks | sub | sup | bot | top), ld >= blockw.
 """
@@ -61,6 +62,17 @@ def make_system(nblocks, blockw, ndiag, family="D", seed=0, ld=None, nsat=0, cou
         prng = np.random.default_rng(7_000_003 * (seed + 1))
         for bi in range(nblocks):
             blk[bi] = blk[bi][:, prng.permutation(w)]  # rows of the column-major block [c, r]
+    elif family == "H":
+        # as R, but the rows are shuffled inside the upper and the lower half of each block separately: every block
+        # pivots, yet no row interchange crosses the middle (the two-SM blockw-32 solve kernel's condition)
+        idx = np.arange(w)
+        d = blk[:, idx, idx]
+        blk[:, idx, idx] = d + np.where(d >= 0, 1.0, -1.0) * w
+        prng = np.random.default_rng(7_000_003 * (seed + 1) + 1)
+        h = w // 2
+        for bi in range(nblocks):
+            perm = np.concatenate([prng.permutation(h), h + prng.permutation(w - h)])
+            blk[bi] = blk[bi][:, perm]
     elif family == "P":
         if w > 1:
             # redraw the (very rare) blocks with a near-tie between pivot candidates; the main stream is untouched
@@ -70,7 +82,7 @@ def make_system(nblocks, blockw, ndiag, family="D", seed=0, ld=None, nsat=0, cou
                 blk[bad] = redraw.uniform(-1.0, 1.0, size=(bad.size, w, w))
                 bad = bad[min_pivot_gap(blk[bad]) < PIVOT_GAP]
     else:
-        raise ValueError("family must be 'D', 'P' or 'R'")
+        raise ValueError("family must be 'D', 'P', 'R' or 'H'")
     n_all = _ndata(nblocks, blockw, ndiag, nsat, ld)
     data = np.zeros(n_all)
     nblk = nblocks * w * ld

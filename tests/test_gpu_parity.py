@@ -96,7 +96,7 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9}
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9, "half32": 10}
 
 
 @pytest.fixture(params=list(PATHS))
@@ -357,3 +357,60 @@ def test_many_rhs_wavefront_repeatable():
             L.bdilu_debug_force_chain_solve(old)
         rel = float(((first - ref).abs().amax(dim=-1) / ref.abs().amax(dim=-1)).max())
         assert rel < 1e-12
+
+
+@pytest.mark.parametrize("N,d,ld", [(64, 1, 32), (200, 2, 32), (333, 3, 34), (67, 4, 32), (2048, 2, 32)])
+def test_two_sm_blockw32_kernel(oracle, N, d, ld):
+    """bdilu_solve_half32.cu (rows 0..15 / 16..31 of every block on the two CTAs of a cluster): identity permutations
+    (D), pivoting confined to the halves (H: non-trivial colbyrow inside the kernel), and systems that pivot across
+    the middle (R, P: handed to quad32 through the status array) -- alone and mixed in one batch."""
+    from block_diag_ilu_b200 import _lib
+    L = _lib.lib()
+    old = L.bdilu_debug_force_chain_solve(PATHS["half32"])
+    try:
+        run_case(oracle, 2, N, 32, d, "D", ld=ld, nrhs=2, seed0=51)
+        run_case(oracle, 2, N, 32, d, "H", ld=ld, nrhs=1, seed0=52)
+        run_case(oracle, 1, N, 32, d, "R", ld=ld, nrhs=2, seed0=53)
+        # mixed batch: systems 0 and 2 stay on the two-SM kernel, systems 1 and 3 go to quad32
+        parts = [synth.make_batch(1, N, 32, d, fam, seed0=60 + k, ld=ld, nrhs=2) for k, fam in enumerate("DRHP")]
+        data = np.concatenate([p[0] for p in parts])
+        b = np.concatenate([p[1] for p in parts])
+        ilu = dev.BatchedILU(torch.from_numpy(data).cuda(), N, 32, d, ld=ld, copy=True)
+        x = ilu.solve(torch.from_numpy(b).cuda()).cpu().numpy()
+        L.bdilu_debug_force_chain_solve(PATHS["chain"])
+        xc = ilu.solve(torch.from_numpy(b).cuda()).cpu().numpy()
+        assert int(ilu.flags.abs().max()) == 0
+        assert np.abs(x - xc).max() <= 1e-12 * np.abs(xc).max()
+    finally:
+        L.bdilu_debug_force_chain_solve(old)
+
+
+def test_two_sm_blockw32_kernel_flags(oracle):
+    """NaN in b and a zero U diagonal in either half give the reference's return values on the two-SM kernel."""
+    from block_diag_ilu_b200 import _lib
+    L = _lib.lib()
+    N, w, d = 96, 32, 2
+    data, b = synth.make_batch(1, N, w, d, "D", seed0=71)
+    old = L.bdilu_debug_force_chain_solve(PATHS["half32"])
+    try:
+        ilu = dev.BatchedILU(torch.from_numpy(data).cuda(), N, w, d, copy=True)
+        fac = data[0].copy()
+        _, rbc, cbr, _ = oracle.factor(fac, N, w, d, 0, w)
+        for pos in (5 * w + 3, 5 * w + 20, 70 * w + 31):     # upper half, lower half, last row of a block
+            bn = b.copy()
+            bn[0, 0, pos] = np.nan
+            ilu.solve(torch.from_numpy(bn).cuda())
+            _, flag = oracle.solve(fac, N, w, d, 0, w, rbc, cbr, bn[0, 0])
+            assert int(ilu.flags[0, 0]) == flag == pos + 1
+        for (blk, row) in ((7, 2), (7, 25)):
+            saved = float(ilu.data[0, (blk * w + row) * w + row])
+            ilu.data[0, (blk * w + row) * w + row] = 0.0
+            keep = fac[(blk * w + row) * w + row]
+            fac[(blk * w + row) * w + row] = 0.0      # in place: the reference's ILU_inplace holds a pointer to this buffer
+            ilu.solve(torch.from_numpy(b).cuda())
+            _, flag = oracle.solve(fac, N, w, d, 0, w, rbc, cbr, b[0, 0])
+            assert int(ilu.flags[0, 0]) == flag == N * w + blk * w + row
+            fac[(blk * w + row) * w + row] = keep
+            ilu.data[0, (blk * w + row) * w + row] = saved
+    finally:
+        L.bdilu_debug_force_chain_solve(old)
