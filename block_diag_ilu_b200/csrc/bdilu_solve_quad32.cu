@@ -40,8 +40,14 @@ using namespace wave;  // mbarrier / bulk-copy / volatile shared-memory helpers,
 #endif
 constexpr int W = 32;
 constexpr int G = 4;    // blocks per stage group
-constexpr int NP = 2;   // producer warps
-constexpr int QW = 14;  // consumer warps: QW + NP = 16 warps = 4 per scheduler, so each thread may hold 128 registers
+#ifndef Q32_NP
+#define Q32_NP 2
+#endif
+#ifndef Q32_QW
+#define Q32_QW 13  // measured on cfg3 (solve ms): 10: 2.73, 11: 2.63, 12: 2.57, 13: 2.56, 14: 2.59, 15 with one producer: 2.94
+#endif
+constexpr int NP = Q32_NP;   // producer warps
+constexpr int QW = Q32_QW;  // consumer warps (QW + NP <= 16 warps, so each thread may hold 128 registers)
 constexpr int RS = 32;  // ring slots (power of two, >= QW + MAXD + 1: see the reset protocol below)
 static_assert(QW + MAXD + 1 <= RS, "ring too small for the reset protocol");
 
