@@ -80,9 +80,32 @@ __device__ __forceinline__ void issue_stage(unsigned slot, const Front<ND> &F, i
     constexpr unsigned IS = WARPS * 32 * 8;  // bytes between items
     const int ldk = TIGHT ? WP : ld;
     const bool ok = rowok && inrange;
+    if (TIGHT && WP >= 4) {
+        // tight blocks: the block is copied as an image, 16 bytes per lane and instruction, so that an instruction
+        // touches one whole 128-byte line per group (at blockw 8) instead of half a line twice: the copies of a warp
+        // are bound by the number of distinct lines they touch (~9 cycles each, scratch/pf_prof.py).  The first WP items
+        // of the stage hold the images of the CTA's groups back to back; lanes read each other's copies after the barrier
+        // in read_stage.
+        // The rows (= columns of the block) of the image are rotated by the group index modulo 128 bytes' worth of rows, so
+        // that the groups of a warp read from different banks (images are a multiple of 128 bytes apart).
+        constexpr int ROT = (WP < 16) ? 16 / WP : 1;
+        const unsigned g = threadIdx.x / WP;
+        const unsigned img = slot - (threadIdx.x * 8u) + g * (WP * WP * 8u);  // my group's image
+        const unsigned rot = g % ROT;
+        const char *src = reinterpret_cast<const char *>(F.blk - r);
 #pragma unroll
-    for (int k = 0; k < WP; ++k) cp_async8(slot + k * IS, F.blk + (int64_t)k * ldk, ok && (TIGHT || k < w));
-    if (!FWD) cp_async8(slot + WP * IS, F.blk + (int64_t)r * ldk, ok);
+        for (int t = 0; t < WP / 2; ++t) {
+            const unsigned e = 2u * (unsigned)(t * WP + r);            // first of the two elements of my chunk
+            const unsigned kd = ((e / WP) + rot) & (WP - 1);           // image row it goes to
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(img + (kd * WP + (e % WP)) * 8u), "l"(src + e * 8u),
+                         "r"(ok ? 16 : 0)
+                         : "memory");
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < WP; ++k) cp_async8(slot + k * IS, F.blk + (int64_t)k * ldk, ok && (TIGHT || k < w));
+        if (!FWD) cp_async8(slot + WP * IS, F.blk + (int64_t)r * ldk, ok);
+    }
     cp_async8(slot + (WP + 1) * IS, F.vec, ok);
 #pragma unroll
     for (int d = 0; d < ND; ++d) {
@@ -94,13 +117,23 @@ __device__ __forceinline__ void issue_stage(unsigned slot, const Front<ND> &F, i
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-template <int WP, int ND, bool FWD>
-__device__ __forceinline__ void read_stage(Stage<WP, ND> &S, const double *slot)
+template <int WP, int ND, bool FWD, bool TIGHT>
+__device__ __forceinline__ void read_stage(Stage<WP, ND> &S, const double *slot, int r)
 {
     constexpr int IS = WARPS * 32;  // doubles between items
+    if (TIGHT && WP >= 4) {
+        __syncwarp();  // the image was copied by all lanes of my group (each waited for its own copies)
+        constexpr int ROT = (WP < 16) ? 16 / WP : 1;
+        const int g = threadIdx.x / WP, rot = g % ROT;
+        const double *img = slot - threadIdx.x + g * (WP * WP);
 #pragma unroll
-    for (int k = 0; k < WP; ++k) S.m[k] = slot[k * IS];
-    S.dg = FWD ? 1.0 : slot[WP * IS];
+        for (int k = 0; k < WP; ++k) S.m[k] = img[((k + rot) & (WP - 1)) * WP + r];
+        S.dg = FWD ? 1.0 : img[((r + rot) & (WP - 1)) * WP + r];
+    } else {
+#pragma unroll
+        for (int k = 0; k < WP; ++k) S.m[k] = slot[k * IS];
+        S.dg = FWD ? 1.0 : slot[WP * IS];
+    }
     S.vec = slot[(WP + 1) * IS];
 #pragma unroll
     for (int d = 0; d < ND; ++d) S.cf[d] = slot[(WP + 2 + d) * IS];
@@ -196,7 +229,7 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                 Stage<WP, ND> S;
                 PF_T(t0);
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");
-                read_stage<WP, ND, true>(S, myslot + s * STAGE);
+                read_stage<WP, ND, true, TIGHT>(S, myslot + s * STAGE, r);
                 PF_T(t1);
                 double acc = group_bcast<G>(S.vec, S.rbc);
                 if (rowok && isnan(acc)) nan_first = min(nan_first, bi * w + S.rbc + 1);
@@ -231,7 +264,7 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                 for (int d = ND - 1; d > 0; --d) prev[d] = prev[d - 1];
                 prev[0] = acc;
                 issue_stage<WP, ND, true, TIGHT>(myslot_s + s * STAGE * 8u, F, w, ld, N, r, rowok, bi + PF < N);
-                prefetch_far<ND, true>(F, w, blk_step, ld, N, r, nlines, PD);
+                if (PD > 0) prefetch_far<ND, true>(F, w, blk_step, ld, N, r, nlines, PD);
                 advance<ND, true>(F, w, blk_step, ld);
                 PF_T(t4);
                 PF_ADD(0, t0, t1); PF_ADD(1, t1, t2); PF_ADD(2, t2, t3); PF_ADD(3, t3, t4); PF_ADD(4, 0, 1);
@@ -265,7 +298,7 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                 const int bi = N - 1 - i;
                 Stage<WP, ND> S;
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");
-                read_stage<WP, ND, false>(S, myslot + s * STAGE);
+                read_stage<WP, ND, false, TIGHT>(S, myslot + s * STAGE, r);
                 // x[r] = (y[r] - sum U[r][k] x[k]) / U[r][r] (:524-532) with the division off the chain: my row, its
                 // coupling coefficients and y[r] are scaled by 1/U[r][r] while the predecessors still work (as the
                 // blockw-32 kernel does), so a row costs one shuffle and one FMA.  Not the reference's rounding sequence
@@ -305,7 +338,7 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                 for (int d = ND - 1; d > 0; --d) prev[d] = prev[d - 1];
                 prev[0] = acc;
                 issue_stage<WP, ND, false, TIGHT>(myslot_s + s * STAGE * 8u, F, w, ld, N, r, rowok, i + PF < N);
-                prefetch_far<ND, false>(F, w, blk_step, ld, N, r, nlines, PD);
+                if (PD > 0) prefetch_far<ND, false>(F, w, blk_step, ld, N, r, nlines, PD);
                 advance<ND, false>(F, w, blk_step, ld);
             }
         }
@@ -340,7 +373,8 @@ static cudaError_t launch_w(const double *data, int64_t sys_stride, int nsys, co
     const int64_t total = (int64_t)nsys * V.nrhs;
     const int64_t per_cta = (int64_t)WARPS * (32 / WP);
     const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);
-    const bool tight = D.w == WP && D.ld == WP;
+    // tight blocks are copied as 16-byte chunks: the blocks of every system must then sit on 16-byte boundaries
+    const bool tight = D.w == WP && D.ld == WP && (reinterpret_cast<uintptr_t>(data) & 15) == 0 && (sys_stride & 1) == 0;
 #define PF_GO(ND)                                                                                                       \
     return tight ? launch_one<WP, ND, PF, true>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st) \
                  : launch_one<WP, ND, PF, false>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st)
