@@ -326,10 +326,8 @@ def kernel_names(w, workload, nsys, nrhs):
         sk = "solve_mrhs_wave_kernel<64,"
     elif w == 32 and workload == "cfg3":
         sk = "solve_quad32_kernel<"
-    elif nrhs < 8 and (w <= 4 or nsys * nrhs >= (384 if w <= 8 else 128)):
-        sk = "pf::solve_chain_pf_kernel<%d," % wp     # prefetched narrow-block chain kernel (csrc/bdilu_solve_pf.cu)
     else:
-        sk = "solve_mrhs_wave_kernel<%d," % wp          # wavefront groups (few chains of narrow blocks)
+        sk = "pf::solve_chain_pf_kernel<%d," % wp     # prefetched narrow-block chain kernel (csrc/bdilu_solve_pf.cu)
     return fk, sk
 
 

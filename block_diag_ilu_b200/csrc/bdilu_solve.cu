@@ -213,24 +213,21 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
     const int64_t total = (int64_t)nsys * V.nrhs;
     if (total == 0 || D.nblocks == 0) return cudaSuccess;
     cudaError_t werr;
-    // Narrow blocks (bdilu_solve_pf.cu).  Measured on B200 (scratch/pf_time.py; ms, one vector per system, this kernel
-    // against the previous choice):
-    //   blockw 4, N = 64:    1 system 0.065 / 0.10 (cfg1);  4096: 0.07 / 0.16;  100000: 1.2 / 0.8 (general chain kernel)
-    //   blockw 8, N = 512:   64: 0.58 / 0.53 (wavefront groups);  512: 0.58 / 0.74;  1024: 0.58 / 1.36;  2048: 0.61 / 1.76;
-    //                        4096: 1.0 / 2.4 (cfg5)
-    //   blockw 16, N = 1024: 1: 1.06 / 1.05;  296: 1.10 / 1.25;  1200: 1.67 / 3.6
-    // so it takes the batches beyond a few hundred chains, everything small at blockw <= 4, and (below) every shape it
-    // fits that would otherwise fall to the general chain kernel.  Batches of 8 or more vectors per system stay with the
-    // many-vector kernels, which read each block once per group of vectors.
+    // Narrow blocks (bdilu_solve_pf.cu).  Measured on B200 (scratch/pf_time.py; ms, this kernel against the previous
+    // choice among the wavefront-group / many-vector / general kernels):
+    //   blockw 4, N = 64:    1 system 0.053 / 0.10 (cfg1);  4096: 0.07 / 0.16
+    //   blockw 8, N = 512:   1..64 systems 0.39 / 0.54;  256: 0.39 / 0.60;  2048: 0.41 / 1.76;  4096: 0.75 / 2.4 (cfg5);
+    //                        4096 x 8 vectors 3.1 / 3.5;  1 system, N = 4096: 2.9 / 4.1
+    //   blockw 16, N = 1024: 1..296 systems 1.04 / 1.05-1.25 (cfg2);  1200: 1.18 / 3.6;  16 x 64 vectors 1.09 / 1.26
+    // so it is the first choice wherever it fits, except for big batches of many vectors per system, where the many-vector
+    // kernels read each block once per group of vectors instead of once per vector, and huge batches of tiny systems.
     // With satellites (nsat > 0, which the wavefront and many-vector kernels decline) it also covers blockw <= 32.
     const bool pf_shape = D.ndiag >= 1 && D.ndiag <= 4 && D.w >= 2 && D.w <= (D.nsat > 0 ? 32 : 16);
     bool pf_first = g_solve_path == 9;
     if (g_solve_path == 0 && pf_shape) {
-        const bool groups_fit = D.w >= 4 && !(D.w & 3);  // shapes the group / wavefront kernels accept at all
-        if (D.nsat > 0) pf_first = true;
-        else if (D.w <= 4) pf_first = !(groups_fit && V.nrhs >= 8) && total <= 20000;
-        else if (!groups_fit || D.nblocks < 128) pf_first = V.nrhs < 8 || !groups_fit;
-        else pf_first = V.nrhs < 8 && total >= (D.w <= 8 ? 384 : 128) * (int64_t)sm_count() / 148;
+        const bool groups_fit = D.nsat == 0 && D.w >= 4 && !(D.w & 3);  // shapes the many-vector kernels accept at all
+        const bool many = groups_fit && V.nrhs >= 8 && total > 64 * (int64_t)sm_count();
+        pf_first = !many && (D.w > 4 || total <= 20000);
     }
     if (pf_first && try_launch_solve_pf(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr)) return werr;
     if (try_launch_solve_mrhs(data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st, &werr)) return werr;

@@ -193,7 +193,7 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
     const int64_t blk_step = (int64_t)w * ld;
     const int nlines = (int)((blk_step * 8 + 127) / 128);  // <= 16 at blockw 16 with ld = 16; wider ld: the first G lines only
 #ifndef BDILU_PF_FAR
-#define BDILU_PF_FAR 12
+#define BDILU_PF_FAR 0  // far L2 prefetch (blocks ahead of the ring): measured, and off -- its up to 32 line requests per block cost more than the DRAM latency they hide (cfg5 per GPU at 2 GPUs: 0.62 -> 0.41 ms without)
 #endif
     constexpr int PD = BDILU_PF_FAR;
 
