@@ -414,7 +414,7 @@ __device__ __forceinline__ bool eliminate_diag_small(double (&a)[WP], double (*u
 // here a lane reads only its half of the pivot row and uses each element for two rows, and the two pivot-row lanes
 // publish 8 + 8 doubles instead of one lane publishing 32.  The multipliers of column k are formed by the 16 lanes that
 // hold it and handed to their row partners by shuffle.  The 2-D layout sank an earlier attempt on the GENERAL
-// elimination (two-row pivot bookkeeping, scratch/factor32x2_experiment.patch); with static diagonal pivots there is no
+// elimination (two-row pivot bookkeeping, git show 1850672:scratch/factor32x2_experiment.patch); with static diagonal pivots there is no
 // bookkeeping left.  Element for element the operations are those of eliminate_diag32 without its pairing (each update
 // a -= l*u is one fma with the finished pivot-row value), hence those of the general loop: bit-identical results.
 __device__ __forceinline__ bool eliminate_diag32_grid(double (&t)[2][16], double *mb, double2 *dgs, int lane)

@@ -28,7 +28,7 @@
 // one LDS.64 per step, no address arithmetic.
 // The slots are filled by four LOADER warps through registers (LDG.128 -> STS.64).  TMA was tried first and cannot do
 // it: a request costs ~60 cycles of issue whatever its size, and tensor boxes with 64..288-byte rows ran at
-// ~10 B/cycle (scratch/ub, scratch/skew_tma_version.cu.txt).  The register path stores each column from the row
+// ~10 B/cycle (scratch/ub; the TMA version: git show 1850672:scratch/skew_tma_version.cu.txt).  The register path stores each column from the row
 // below the diagonal on (backward: from the row above it, reversed), 16-byte aligned and skewed so that the consumers'
 // LDS.128 are conflict free, with zero padding that never has to be rewritten.  Blocks outside the system are
 // clamped to a real block and given zero right-hand sides and coefficients, which makes the ramp-up and the tail
