@@ -37,7 +37,8 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
 extern int g_solve_path;  // test hook (7 = quad32; 8 = experimental systolic blockw-32 kernel first, quad32 behind it): 0 = automatic, 1 = chain kernel, 2 = generic wavefront kernel, 3 = one-row wave32 kernel,
                           // 4 = many-vector kernel (one warp per group) whenever the shape allows it, 5 = automatic without the many-vector
                           // kernels, 6 = many-vector kernels (wavefront form where it applies) whenever the shape allows it,
-                          // 9 = prefetched narrow-block chain kernel (bdilu_solve_pf.cu) whenever the shape allows it,
+                          // 9 = prefetched narrow-block chain kernel (bdilu_solve_pf.cu) whenever the shape allows it (11 / 12: the same with four rows /
+                          // one row per shuffle round forced),
                           // 10 = two-SM blockw-32 kernel (bdilu_solve_half32.cu) first, quad32 behind it, whatever the batch size
 // many right-hand sides per factor: a warp carries 8 vectors, blocks staged once per CTA (bdilu_solve_mrhs.cu)
 bool try_launch_solve_mrhs(const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,

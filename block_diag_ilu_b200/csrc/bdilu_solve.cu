@@ -223,7 +223,7 @@ cudaError_t launch_solve(const double *data, int64_t sys_stride, int nsys, const
     // kernels read each block once per group of vectors instead of once per vector, and huge batches of tiny systems.
     // With satellites (nsat > 0, which the wavefront and many-vector kernels decline) it also covers blockw <= 32.
     const bool pf_shape = D.ndiag >= 1 && D.ndiag <= 4 && D.w >= 2 && D.w <= (D.nsat > 0 ? 32 : 16);
-    bool pf_first = g_solve_path == 9;
+    bool pf_first = g_solve_path == 9 || g_solve_path == 11 || g_solve_path == 12;
     if (g_solve_path == 0 && pf_shape) {
         const bool groups_fit = D.nsat == 0 && D.w >= 4 && !(D.w & 3);  // shapes the many-vector kernels accept at all
         const bool many = groups_fit && V.nrhs >= 8 && total > 64 * (int64_t)sm_count();

@@ -20,6 +20,9 @@ namespace bdilu {
 namespace pf {
 
 constexpr int WARPS = 2;
+#ifndef PF_QUAD_WARPS_PER_SM
+#define PF_QUAD_WARPS_PER_SM 8
+#endif
 
 // Phase profile (debug builds only, -DBDILU_PF_PROF): cycles of warp 0 of CTA 0, forward sweep:
 //   [0] wait_group + ring -> registers  [1] b gather + couplings  [2] the rows  [3] store, copies of the next block,
@@ -171,7 +174,7 @@ __device__ __forceinline__ void advance(Front<ND> &F, int w, int64_t blk_step, i
     }
 }
 
-template <int WP, int ND, int PF, bool TIGHT>
+template <int WP, int ND, int PF, bool TIGHT, bool QUADS>
 __global__ void __launch_bounds__(WARPS * 32)
 solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int nsys, Dims D,
                       const int *__restrict__ rowbycol, const int *__restrict__ colbyrow,
@@ -249,12 +252,39 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                             acc = fma(-__ldg(sd + D.off_bot + D.sat_chunk(N + bci - bi - 1, bci) + S.cbr), x[bci * w + S.cbr], acc);
                 }
                 PF_T(t2);
+                if constexpr (QUADS && TIGHT && WP >= 4) {
+                    // four rows per shuffle round: the four accumulators and the six entries of the 4 x 4 triangle that
+                    // couples them are broadcast together, every lane resolves the triangle redundantly (the same fmas, in
+                    // the same order, as the owners would do one row at a time) and applies the four finished values.
+                    // One dependent shuffle per four rows instead of four: ~25 instead of ~41 cycles per row, twice the
+                    // instructions -- for batches that leave the SMs mostly idle (the chain's latency is the run time).
 #pragma unroll
-                for (int k = 0; k < WP; ++k) {
-                    if (TIGHT || k < w) {
-                        const double yk = group_bcast<G>(acc, k);
-                        const double t = fma(-S.m[k], yk, acc);
+                    for (int k = 0; k < WP; k += 4) {
+                        const double y0 = group_bcast<G>(acc, k);
+                        const double a1 = group_bcast<G>(acc, k + 1), a2 = group_bcast<G>(acc, k + 2), a3 = group_bcast<G>(acc, k + 3);
+                        const double m10 = group_bcast<G>(S.m[k], k + 1), m20 = group_bcast<G>(S.m[k], k + 2);
+                        const double m30 = group_bcast<G>(S.m[k], k + 3), m21 = group_bcast<G>(S.m[k + 1], k + 2);
+                        const double m31 = group_bcast<G>(S.m[k + 1], k + 3), m32 = group_bcast<G>(S.m[k + 2], k + 3);
+                        const double y1 = fma(-m10, y0, a1);
+                        const double y2 = fma(-m21, y1, fma(-m20, y0, a2));
+                        const double y3 = fma(-m32, y2, fma(-m31, y1, fma(-m30, y0, a3)));
+                        double t = fma(-S.m[k], y0, acc);
                         acc = (r > k) ? t : acc;
+                        t = fma(-S.m[k + 1], y1, acc);
+                        acc = (r > k + 1) ? t : acc;
+                        t = fma(-S.m[k + 2], y2, acc);
+                        acc = (r > k + 2) ? t : acc;
+                        t = fma(-S.m[k + 3], y3, acc);
+                        acc = (r > k + 3) ? t : acc;
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < WP; ++k) {
+                        if (TIGHT || k < w) {
+                            const double yk = group_bcast<G>(acc, k);
+                            const double t = fma(-S.m[k], yk, acc);
+                            acc = (r > k) ? t : acc;
+                        }
                     }
                 }
                 PF_T(t3);
@@ -322,14 +352,37 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
                             acc = fma(-(__ldg(sd + D.off_top + D.sat_chunk(sati - 1, bi) + S.cbr) * rinv),
                                       x[(N - sati + bi) * w + S.cbr], acc);
                 }
+                if constexpr (QUADS && TIGHT && WP >= 4) {
 #pragma unroll
-                for (int kr = 0; kr < WP; ++kr) {
-                    const int k = WP - 1 - kr;
-                    if (TIGHT || k < w) {
-                        const double mk = S.m[k] * rinv;
-                        const double xk = group_bcast<G>(acc, k);
-                        const double t = fma(-mk, xk, acc);
+                    for (int kq = 0; kq < WP; kq += 4) {
+                        const int k = WP - 1 - kq;  // rows k, k-1, k-2, k-3
+                        const double s0 = S.m[k] * rinv, s1 = S.m[k - 1] * rinv, s2 = S.m[k - 2] * rinv, s3 = S.m[k - 3] * rinv;
+                        const double x0 = group_bcast<G>(acc, k);
+                        const double a1 = group_bcast<G>(acc, k - 1), a2 = group_bcast<G>(acc, k - 2), a3 = group_bcast<G>(acc, k - 3);
+                        const double c10 = group_bcast<G>(s0, k - 1), c20 = group_bcast<G>(s0, k - 2), c30 = group_bcast<G>(s0, k - 3);
+                        const double c21 = group_bcast<G>(s1, k - 2), c31 = group_bcast<G>(s1, k - 3), c32 = group_bcast<G>(s2, k - 3);
+                        const double x1 = fma(-c10, x0, a1);
+                        const double x2 = fma(-c21, x1, fma(-c20, x0, a2));
+                        const double x3 = fma(-c32, x2, fma(-c31, x1, fma(-c30, x0, a3)));
+                        double t = fma(-s0, x0, acc);
                         acc = (r < k) ? t : acc;
+                        t = fma(-s1, x1, acc);
+                        acc = (r < k - 1) ? t : acc;
+                        t = fma(-s2, x2, acc);
+                        acc = (r < k - 2) ? t : acc;
+                        t = fma(-s3, x3, acc);
+                        acc = (r < k - 3) ? t : acc;
+                    }
+                } else {
+#pragma unroll
+                    for (int kr = 0; kr < WP; ++kr) {
+                        const int k = WP - 1 - kr;
+                        if (TIGHT || k < w) {
+                            const double mk = S.m[k] * rinv;
+                            const double xk = group_bcast<G>(acc, k);
+                            const double t = fma(-mk, xk, acc);
+                            acc = (r < k) ? t : acc;
+                        }
                     }
                 }
                 if (live && rowok) *xo = acc;
@@ -353,16 +406,16 @@ solve_chain_pf_kernel(const double *__restrict__ data, int64_t sys_stride, int n
         flags[gid] = (nan_first != 0x7fffffff) ? nan_first : (zero_last >= 0 ? N * w + zero_last : 0);
 }
 
-template <int WP, int ND, int PF, bool TIGHT>
+template <int WP, int ND, int PF, bool TIGHT, bool QUADS>
 static cudaError_t launch_one(unsigned grid, const double *data, int64_t sys_stride, int nsys, const Dims &D, const int *rowbycol,
                               const int *colbyrow, const double *b, double *x, const VecLayout &V, int *flags, cudaStream_t st)
 {
     const size_t smem = (size_t)PF * Ring<WP, ND>::NITEM * WARPS * 32 * sizeof(double);
-    cudaError_t e = cudaFuncSetAttribute(solve_chain_pf_kernel<WP, ND, PF, TIGHT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);  // per (function, device): set on every launch
+    cudaError_t e = cudaFuncSetAttribute(solve_chain_pf_kernel<WP, ND, PF, TIGHT, QUADS>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  // per (function, device)
     if (e != cudaSuccess) return e;
-    solve_chain_pf_kernel<WP, ND, PF, TIGHT><<<grid, WARPS * 32, smem, st>>>(data, sys_stride, nsys, D, rowbycol, colbyrow, b,
-                                                                            x, V, flags);
+    solve_chain_pf_kernel<WP, ND, PF, TIGHT, QUADS><<<grid, WARPS * 32, smem, st>>>(data, sys_stride, nsys, D, rowbycol, colbyrow,
+                                                                                   b, x, V, flags);
     return cudaGetLastError();
 }
 
@@ -375,9 +428,16 @@ static cudaError_t launch_w(const double *data, int64_t sys_stride, int nsys, co
     const unsigned grid = (unsigned)((total + per_cta - 1) / per_cta);
     // tight blocks are copied as 16-byte chunks: the blocks of every system must then sit on 16-byte boundaries
     const bool tight = D.w == WP && D.ld == WP && (reinterpret_cast<uintptr_t>(data) & 15) == 0 && (sys_stride & 1) == 0;
-#define PF_GO(ND)                                                                                                       \
-    return tight ? launch_one<WP, ND, PF, true>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st) \
-                 : launch_one<WP, ND, PF, false>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st)
+    // four rows per shuffle round while the chains' latency is the run time (few warps per SM); one row per round once
+    // the batch fills the SMs' load/store pipe (the quad form issues 20 shuffles per 4 rows instead of 8)
+    const int64_t warps = (total * WP + 31) / 32;
+    // (test hooks 11 / 12 of bdilu_debug_force_chain_solve force four rows / one row per round)
+    const bool quads = tight && WP >= 4 &&
+                       (g_solve_path == 11 || (g_solve_path != 12 && warps <= (int64_t)PF_QUAD_WARPS_PER_SM * sm_count()));
+#define PF_GO(ND)                                                                                                              \
+    return !tight ? launch_one<WP, ND, PF, false, false>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st) \
+           : quads ? launch_one<WP, ND, PF, true, true>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st)  \
+                   : launch_one<WP, ND, PF, true, false>(grid, data, sys_stride, nsys, D, rowbycol, colbyrow, b, x, V, flags, st)
     switch (D.ndiag) {
     case 1: PF_GO(1);
     case 2: PF_GO(2);

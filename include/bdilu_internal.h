@@ -18,7 +18,8 @@ extern "C" {
  * kernel; 4 / 6 = many-vector kernels (one warp per group / wavefront form) whenever the shape allows; 5 = automatic
  * without the many-vector kernels; 7 = same as 0 at blockw 32 (quad32); 8 = blockw 32: experimental systolic kernel first, quad32 behind it for the
  * vectors it hands back (csrc/bdilu_solve_skew.cu; slower than quad32 on B200, kept for the record); 9 = prefetched narrow-block
- * chain kernel (csrc/bdilu_solve_pf.cu) whenever the shape allows it; 10 = blockw 32: experimental two-SMs-per-chain kernel first
+ * chain kernel (csrc/bdilu_solve_pf.cu) whenever the shape allows it (11 / 12: the same with four rows / one row per shuffle round
+ * forced); 10 = blockw 32: experimental two-SMs-per-chain kernel first
  * (csrc/bdilu_solve_half32.cu), quad32 behind it for the systems that pivoted across the middle of a block.
  * Every path is parity-tested.  Returns the previous setting. */
 BDILU_API int bdilu_debug_force_chain_solve(int on);

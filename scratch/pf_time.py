@@ -17,7 +17,7 @@ for (nsys, N, w, d, nrhs) in CASES:
     data, b = synth.make_batch_device(nsys, N, w, d, torch.device("cuda:0"), seed=5, nrhs=nrhs)
     ilu = dev.BatchedILU(data, N, w, d)
     res, xs = {}, {}
-    for name, path in (("auto", 0), ("pf", 9), ("chain", 1)):
+    for name, path in (("auto", 0), ("pf", 12), ("pf4", 11), ("chain", 1)):
         old = L.bdilu_debug_force_chain_solve(path)
         best = 1e9
         for _ in range(4):
@@ -26,8 +26,9 @@ for (nsys, N, w, d, nrhs) in CASES:
             best = min(best, e1.elapsed_time(e2))
         L.bdilu_debug_force_chain_solve(old)
         res[name], xs[name] = best, x
+    same4 = bool(torch.equal(xs["pf"], xs["pf4"]))
     same = float(((xs["pf"] - xs["chain"]).abs().amax(dim=-1) / xs["chain"].abs().amax(dim=-1)).max())
     print("nsys %d N %d w %d d %d nrhs %d : " % (nsys, N, w, d, nrhs) + "  ".join("%s %.3f ms" % kv for kv in res.items()) +
-          "  | pf vs chain max rel diff: %.2e" % same, flush=True)
+          "  | pf vs chain max rel diff: %.2e, pf4 bit-identical to pf: %s" % (same, same4), flush=True)
     del data, b, ilu, xs, x
     torch.cuda.empty_cache()

@@ -96,7 +96,7 @@ def test_config2_shape(oracle, fam):
     run_case(oracle, 1, 1024, 16, 1, fam, yardstick=(fam == "P"))
 
 
-PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9, "half32": 10}
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9, "half32": 10, "pf_quads": 11, "pf_rows": 12}
 
 
 @pytest.fixture(params=list(PATHS))
