@@ -414,3 +414,29 @@ def test_two_sm_blockw32_kernel_flags(oracle):
             ilu.data[0, (blk * w + row) * w + row] = saved
     finally:
         L.bdilu_debug_force_chain_solve(old)
+
+
+@pytest.mark.parametrize("N,w,d", [(40, 8, 2), (33, 16, 1), (64, 4, 1), (20, 32, 2)])
+def test_misaligned_batches(oracle, N, w, d):
+    """A batch whose systems start on odd 8-byte boundaries (a view into a larger tensor: data pointer 8 mod 16, odd
+    system stride): the kernels that copy 16-byte chunks (narrow-block images, bulk copies) must decline or take their
+    8-byte paths, and the results must not change."""
+    nsys, nrhs = 3, 2
+    data, b = synth.make_batch(nsys, N, w, d, "R", seed0=91, nrhs=nrhs)
+    nd = data.shape[1]
+    big = torch.zeros((nsys, nd + 3), dtype=torch.float64, device="cuda")
+    view = big[:, 1:1 + nd]
+    view.copy_(torch.from_numpy(data))
+    assert view.data_ptr() % 16 == 8 and view.stride(0) % 2 == 1
+    ilu = dev.BatchedILU(view, N, w, d)          # in place on the view
+    x = ilu.solve(torch.from_numpy(b).cuda()).cpu().numpy()
+    assert float(big[:, 0].abs().max()) == 0.0 and float(big[:, nd + 1:].abs().max()) == 0.0   # nothing written outside
+    for s in range(nsys):
+        ref = data[s].copy()
+        ipiv, rbc, cbr, info = oracle.factor(ref, N, w, d, 0, w)
+        assert np.array_equal(ilu.ipiv[s].cpu().numpy(), ipiv)
+        assert block_rel_err(view[s].cpu().numpy(), ref, N, w, w) < TOL
+        for r in range(nrhs):
+            xr, flag = oracle.solve(ref, N, w, d, 0, w, rbc, cbr, b[s, r])
+            assert flag == int(ilu.flags[s, r]) == 0
+            assert np.abs(x[s, r] - xr).max() <= TOL * np.abs(xr).max()
