@@ -581,7 +581,7 @@ struct ScaledSrc {
 };
 
 template <int WP, bool EXACT, bool SCALED>
-__global__ void __launch_bounds__(FACTOR_WARPS * 32, WP == 32 ? 4 : 6)
+__global__ void __launch_bounds__(FACTOR_WARPS * 32, WP == 32 ? 4 : (WP <= 8 ? 10 : 6))  // blockw <= 8: measured on cfg5, CTAs per SM 6: 0.69, 8: 0.61, 10: 0.58, 12: 0.62 ms
 factor_kernel(double *data, int64_t sys_stride, int nsys, Dims D, int *__restrict__ ipiv,
               int *__restrict__ rowbycol, int *__restrict__ colbyrow, int *__restrict__ info, ScaledSrc SS)
 {
