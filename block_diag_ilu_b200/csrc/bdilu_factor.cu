@@ -401,6 +401,7 @@ __device__ __forceinline__ bool eliminate_diag_small(double (&a)[WP], double (*u
             if (2 * m > k) a[2 * m] = fma(-l, u.x, a[2 * m]);
             a[2 * m + 1] = fma(-l, u.y, a[2 * m + 1]);
         }
+        if ((k == 1 || k == WP / 2 - 1) && k + 1 < WP && __any_sync(FULL, viol)) return false;  // pivoting blocks leave early
     }
     __syncwarp();
     const double dg = dgs[r].x;
@@ -465,7 +466,8 @@ __device__ __forceinline__ bool eliminate_diag32_grid(double (&t)[2][16], double
                 }
             }
         }
-        if ((k & 7) == 7 && k + 1 < 32 && __any_sync(FULL, viol)) return false;
+        // blocks that pivot leave early: almost always at the first vote (a matrix that is not dominant shows it at once)
+        if ((k == 1 || (k & 7) == 7) && k + 1 < 32 && __any_sync(FULL, viol)) return false;
     }
     __syncwarp();
     const double dg = dgs[lane].x;  // a zero or out-of-range pivot: the general loop (info, true divisions) takes over
