@@ -119,9 +119,12 @@ def test_reference_recorded_outputs_through_the_c_abi(name):
     ("auto", (8192, 32, 2, 1)),           # quad32, the headline kernel: in-band sentinel ring, counter-free recycling
     ("wave32_onerow", (4096, 32, 2, 1)),
     ("wave_generic", (2048, 16, 1, 1)),
-    ("auto", (1024, 16, 1, 1)),           # cfg2's dispatch
+    ("auto", (1024, 16, 1, 1)),           # cfg2's dispatch: the prefetched narrow-block kernel (cp.async ring, images read across lanes)
+    ("mrhs_wave", (1024, 16, 1, 1)),      # the wavefront-group kernel at cfg2's shape
+    ("pf", (512, 8, 2, 1)),               # cfg5's shape
     ("mrhs_wave", (2048, 64, 3, 16)),
     ("skew32", (4096, 32, 2, 1)),
+    ("half32", (4096, 32, 2, 1)),         # two CTAs per chain: progress words in global memory, fences, throttle
 ])
 def test_wavefront_kernels_repeat_bit_identically(path, shape):
     """200 solves of the same batch: any race in the polling protocols would surface as a differing bit (or a trap)."""

@@ -11,7 +11,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from block_diag_ilu_b200 import _lib, device as dev, synth  # noqa: E402
 from oracle import loader  # noqa: E402
 
-PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8}
+PATHS = {"auto": 0, "chain": 1, "wave_generic": 2, "wave32_onerow": 3, "mrhs": 4, "mrhs_wave": 6, "skew32": 8, "pf": 9, "half32": 10}
 SHAPES = [(2, 130, 32, 2, 1), (1, 70, 64, 3, 16), (20, 129, 8, 2, 1), (1, 200, 16, 1, 1), (3, 40, 4, 1, 2)]
 only = sys.argv[1:] or list(PATHS)
 orc = loader.best()
