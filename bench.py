@@ -399,6 +399,39 @@ def matvec_record(case, peak, steps):
                                        "frac": gbs / peak, "unit": "GB/s"}}
 
 
+def factor_pivoting_record(case, steps):
+    """K1 on a batch that DOES pivot (uniform random blocks: ~87 % non-identity pivots at blockw 32).  The timed family D
+    never pivots and takes the factor kernel's optimistic path; this is what the exact fallback costs (disclosure, not
+    part of the metric).  The batch is generated over the pristine buffer and family D is restored afterwards."""
+    torch = case.torch
+    keep = case.pristine.clone()
+    nblk = case.N * case.w * case.w
+    g = torch.Generator(device=case.pristine.device)
+    g.manual_seed(777)
+    case.pristine[:, :nblk].uniform_(-1.0, 1.0, generator=g)
+    st = torch.cuda.current_stream()
+    ts = []
+    nonid = 0.0
+    for it in range(steps + 2):
+        work = case.pristine.clone()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        ilu = case.dev.BatchedILU(work, case.N, case.w, case.d, check=False)
+        e1.record(st)
+        torch.cuda.synchronize()
+        if it >= 2:
+            ts.append(e0.elapsed_time(e1))
+        ident = torch.arange(1, case.w + 1, device=work.device, dtype=torch.int32).repeat(case.N)
+        nonid = float((ilu.ipiv != ident).float().mean())
+        del work, ilu
+    case.pristine.copy_(keep)
+    del keep
+    return {"workload": workload_string(case.name) + " factor only, uniform random blocks (every block pivots)",
+            "ms": stats_ms(ts), "non_identity_pivots": nonid,
+            "note": "optimistic diagonal-pivot attempt abandoned at its first vote, then the general elimination; includes the "
+                    "allocation of the index arrays by the wrapper"}
+
+
 def e2e_reuse_record(case, nsolves):
     """What an unmodified caller of the reference does with one Jacobian (anyode_iterative.hpp:64-88): one ILU, many
     solves -- bdilu_ilu_create once on host data, then bdilu_ilu_solve from host vectors, all copies inside."""
@@ -638,6 +671,7 @@ def run_ours(args, rank, world, local_rank):
         fl = flush if flush is not None else torch.zeros(40 * 1024 * 1024, dtype=torch.float64, device=device)
         line["matvec"] = matvec_record(case, peak, steps)
         line["e2e_reuse"] = e2e_reuse_record(case, 32)
+        line["factor_pivoting"] = factor_pivoting_record(case, steps)
         for name in ("cfg1", "cfg2", "cfg4"):
             c = DeviceCase(name, 0, WORKLOADS[name][3], device)
             sub[name] = sub_record(c, peak, steps, fl, solve_only=(name == "cfg4"))
